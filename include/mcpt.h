@@ -1,0 +1,161 @@
+/* mcpt.h -- C ABI of libmcpt.so, the B200-native drop-in for the reference's path-sampling
+ * hot path (per-pixel Monte Carlo path sampling over a KD-tree-accelerated triangle scene).
+ *
+ * The entry points are what a binding of the reference's tracer interface would call.
+ * The reference exposes the path as four free functions in namespace PW::Tracer
+ * (CVMCTracer/CVMCTracer/CUDA/CUTracer.h:9-12):
+ *     cudaError_t Initialize();
+ *     cudaError_t CreateGeometry(const PW::FileReader::ObjModel* model);
+ *     cudaError_t DestroyGeometry();
+ *     cudaError_t RenderScene(const PWint sceneID, PWVector3f* hostcolor);
+ * and, on the KD-tree side, as Core::Graphics::OnUpdate() ("one more sample per pixel",
+ * MCRT/QuinEngine/Core/Graphics.hpp:17-20) over the buffer contract CB0 / CSMaterial /
+ * CSTriangle / CSKDTree (MCRT/QuinEngine/Utils/Structure.hpp:186-223).
+ * Compile-time knobs of the reference (CVMCTracer/CVMCTracer/stdafx.h:41-45; depth literal
+ * rtx.hlsl:400; camera GraphicsRTX.cpp:173-184) become fields of mcpt_render_cfg.
+ *
+ * Conventions: plain pointers and sizes only; every call is blocking; 0 = success, non-zero =
+ * error class with the text in mcpt_last_error(); no exception crosses the boundary; the
+ * caller owns every host pointer; the library owns all device memory behind one process-global
+ * context (the reference keeps module-level __device__ globals, CUTracer.cu:30-42).
+ */
+#ifndef MCPT_H
+#define MCPT_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    MCPT_OK = 0,
+    MCPT_ERR_INVALID = 1,   /* bad argument / call order                */
+    MCPT_ERR_IO = 2,        /* file missing or malformed                */
+    MCPT_ERR_CUDA = 3,      /* CUDA runtime error (text in last_error)  */
+    MCPT_ERR_NO_DEVICE = 4, /* no usable GPU: the product has no CPU path */
+    MCPT_ERR_NCCL = 5
+};
+
+/* KD-tree construction rule. */
+enum {
+    MCPT_BUILD_REFERENCE = 0, /* node-for-node the tree of KDTree.hpp:58-287 (parity anchor) */
+    MCPT_BUILD_SAH = 1        /* this library's own O(n log n) SAH builder (same hits, other tree) */
+};
+
+/* Which OBJ/MTL reader semantics mcpt_load_obj follows. */
+enum {
+    MCPT_LOADER_TINYOBJ = 0,  /* tinyobjloader 1.1.1 as used by QuinModel (Structure.hpp:9-12)  */
+    MCPT_LOADER_OBJREADER = 1 /* PW::FileReader::ObjModel (CVMCTracer/.../ObjReader.cpp:8-259)   */
+};
+
+enum {
+    MCPT_RNG_PHILOX = 0,    /* Philox4x32-10 keyed by (pixel, sample, bounce) -- the product stream */
+    MCPT_RNG_REFERENCE = 1  /* rtx.hlsl:61-82 TEA+LCG with the mt19937(1234) frame seeds (GraphicsRTX.cpp:170-171) */
+};
+
+enum {
+    MCPT_FLAG_NEE = 1u,        /* next-event estimation to the emitters at Lambert vertices   */
+    MCPT_FLAG_MOMENTS = 2u,    /* also accumulate per-pixel sum of squares                    */
+    MCPT_FLAG_NO_JITTER = 4u,  /* pixel-corner rays ("bias = 0"), for the intersection gate   */
+    MCPT_FLAG_REF_TRAVERSAL = 8u /* render with the reference-order AABB traversal instead of the KD traversal */
+};
+
+/* Intersection kernels selectable through mcpt_intersect_batch. */
+enum {
+    MCPT_ISECT_REFERENCE = 0, /* rtx.hlsl:144-211 visit order and slab test, strict IEEE arithmetic */
+    MCPT_ISECT_KD = 1         /* front-to-back plane traversal of the compact KD nodes (render path)  */
+};
+
+/* Flat scene tables: exactly the fields of CSTriangle / CSMaterial (Structure.hpp:196-211) and
+ * Geometry::Material/Triangle (CVMCTracer/CVMCTracer/Framework/Geometry.h:14-35). */
+typedef struct mcpt_scene_desc {
+    const float* vertices;     /* 3 floats per vertex                              */
+    int32_t num_vertices;
+    const float* normals;      /* 3 floats per normal                              */
+    int32_t num_normals;
+    const uint32_t* triangles; /* 7 uint32 per triangle: v0 v1 v2 n0 n1 n2 matId   */
+    int32_t num_triangles;
+    const float* materials;    /* 12 floats per material: Ka[3] Kd[3] Ks[3] Ns Tr Ni */
+    int32_t num_materials;
+    int32_t build_mode;        /* MCPT_BUILD_*                                     */
+} mcpt_scene_desc;
+
+typedef struct mcpt_render_cfg {
+    int32_t width, height;
+    int32_t spp;             /* samples per pixel rendered by this call                         */
+    int32_t max_depth;       /* the shader's `depth` (rtx.hlsl:400): RR from max_depth, kill at 3*max_depth */
+    int32_t sample_offset;   /* absolute index of the first sample (spp-split across ranks)     */
+    uint32_t seed;           /* Philox key word                                                 */
+    int32_t rng_mode;        /* MCPT_RNG_*                                                      */
+    uint32_t flags;          /* MCPT_FLAG_*                                                     */
+    float eye[3], at[3], up[3]; /* D3DXMatrixLookAtRH arguments (GraphicsRTX.cpp:175-178)       */
+    float fovy;              /* radians (GraphicsRTX.cpp:183)                                   */
+    float emission_scale;    /* 1 for the KD-tree tracer; the CUDA twin multiplies Ka by ILLUM  */
+} mcpt_render_cfg;
+
+typedef struct mcpt_counters {
+    uint64_t paths;          /* camera paths started by the last render call            */
+    uint64_t rays;           /* intersect invocations (camera + bounce + shadow rays)   */
+    double kernel_ms;        /* device time of the render kernels (CUDA events)         */
+    double total_ms;         /* device time of the whole call incl. reduce and copies   */
+    uint32_t launches;       /* kernels launched by the last call                       */
+    uint32_t reserved;
+} mcpt_counters;
+
+typedef struct mcpt_tree_info {
+    int32_t num_nodes, num_leaves, num_leaf_refs, max_depth;
+    int32_t num_emitter_triangles;
+    double build_seconds;
+    uint64_t device_bytes;   /* nodes + ids + triangle records resident in HBM */
+} mcpt_tree_info;
+
+/* ---- PW::Tracer::Initialize (CUTracer.cu:220-223) ---------------------------------------- */
+int mcpt_initialize(int device);
+int mcpt_shutdown(void);
+
+/* ---- PW::Tracer::CreateGeometry (CUTracer.cu:225-314) ------------------------------------- */
+int mcpt_create_geometry(const mcpt_scene_desc* scene);
+/* readObj + CreateGeometry (CVMCTracer/main.cpp:16-17) or QuinModel + KDTree + upload
+ * (GraphicsRTX.cpp:165-167) in one call. */
+int mcpt_load_obj(const char* obj_path, const char* mtl_base, int loader, int build_mode);
+/* Same from a baked scene container (scenes/ *.mcpt, magic "MCPTSCN1"). */
+int mcpt_load_scene_file(const char* path, int build_mode);
+int mcpt_get_tree_info(mcpt_tree_info* info);
+/* Copies the built tree out in the reference's BFS layout (ShaderResource.hpp:128-179);
+ * any pointer may be NULL. aabb6: 6 floats per node. */
+int mcpt_get_tree(uint32_t* left, uint32_t* right, float* aabb6, uint32_t* split_axis,
+                  float* split_value, uint32_t* leaf_offset, uint32_t* leaf_count, uint32_t* leaf_ids);
+/* Copies the flat scene tables out (after any load); pointers may be NULL; counts = {V,N,T,M}. */
+int mcpt_get_scene(int32_t counts[4], float* vertices, float* normals, uint32_t* triangles, float* materials);
+
+/* ---- PW::Tracer::DestroyGeometry (CUTracer.cu:316-338) ------------------------------------ */
+int mcpt_destroy_geometry(void);
+
+/* ---- PW::Tracer::RenderScene (CUTracer.cu:340-404) / Graphics::OnUpdate x spp -------------- */
+void mcpt_default_render_cfg(mcpt_render_cfg* cfg, int width, int height, int spp, int max_depth);
+/* host_rgb: width*height*3 floats, row-major, top row first, LINEAR MEAN radiance (same layout as
+ * `hostcolor`). host_m2 (optional): mean of squared samples per channel (needs MCPT_FLAG_MOMENTS). */
+int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m2);
+/* Device-resident variant: ADDS this call's samples into caller-owned device buffers
+ * dev_sum / dev_sumsq (width*height float4: r,g,b sums and the sample count in .w) on `stream`
+ * (a cudaStream_t, may be NULL).  Used for spp-split multi-GPU: each rank accumulates its share,
+ * then one reduce of dev_sum combines them. */
+int mcpt_render_accumulate_device(const mcpt_render_cfg* cfg, void* dev_sum, void* dev_sumsq, void* stream);
+
+/* ---- intersection parity hook (rtx.hlsl:144-211 `intersect`) ------------------------------ */
+/* rays: 6 floats {origin, direction} each. tri = -1 on miss (t, beta, gamma = 0 then). */
+int mcpt_intersect_batch(const float* rays, int64_t n, int variant, int32_t* tri, float* t,
+                         float* beta, float* gamma);
+int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, void* dev_tri,
+                                void* dev_t, void* dev_beta, void* dev_gamma, void* stream);
+/* Primary rays of one sample index exactly as the render kernel generates them (6 floats/pixel). */
+int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays);
+
+int mcpt_get_counters(mcpt_counters* out);
+const char* mcpt_last_error(void);
+const char* mcpt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCPT_H */

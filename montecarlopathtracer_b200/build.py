@@ -1,0 +1,75 @@
+"""Builds libmcpt.so (hand-written sm_100a CUDA + C++ host code) in-tree with nvcc/g++.
+
+    python -m montecarlopathtracer_b200.build [--force]
+
+nvcc cross-compiles for sm_100a without a GPU.  Flags that matter:
+  -gencode arch=compute_100a,code=sm_100a   B200 only, no PTX fallback for other parts
+  -fmad=false, no -use_fast_math            IEEE mul/add/div/sqrt, never contracted: the
+                                            intersection gate is bit-exact against the CPU oracle
+  -ffp-contract=off (host)                  the KD builder and the triangle pre-computation must
+                                            round like the reference's x86 build
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIBDIR = os.path.join(HERE, "lib")
+OBJDIR = os.path.join(HERE, "build")
+LIB = os.path.join(LIBDIR, "libmcpt.so")
+CLI = os.path.join(LIBDIR, "mcpt_cli")
+
+NVCC = os.environ.get("MCPT_NVCC", "/usr/local/cuda/bin/nvcc")
+CXX = "/usr/bin/g++"
+CUDA_INC = "/usr/local/cuda/include"
+
+CU_SOURCES = ["launch.cu"]
+CPP_SOURCES = ["kd_build.cpp", "scene_io.cpp", "device_scene.cpp", "obj_loader.cpp", "abi_geometry.cpp", "abi_render.cpp"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-fmad=false",
+              "-Xcompiler", "-fPIC", "-ccbin", CXX]
+CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-Wall", "-I" + CUDA_INC]
+
+
+def _newer(target: str, deps: list[str]) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def _headers() -> list[str]:
+    hs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    hs.append(os.path.join(HERE, "..", "include", "mcpt.h"))
+    hs.append(os.path.abspath(__file__))
+    return hs
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    os.makedirs(LIBDIR, exist_ok=True)
+    os.makedirs(OBJDIR, exist_ok=True)
+    hdrs = _headers()
+    objs = []
+    for src in CU_SOURCES:
+        o = os.path.join(OBJDIR, src + ".o")
+        objs.append(o)
+        if force or _newer(o, [os.path.join(CSRC, src)] + hdrs):
+            cmd = [NVCC] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", o]
+            if verbose:
+                cmd.insert(1, "-Xptxas=-v")
+            subprocess.check_call(cmd)
+    for src in CPP_SOURCES:
+        o = os.path.join(OBJDIR, src + ".o")
+        objs.append(o)
+        if force or _newer(o, [os.path.join(CSRC, src)] + hdrs):
+            subprocess.check_call([CXX] + CXX_FLAGS + ["-c", os.path.join(CSRC, src), "-o", o])
+    if force or _newer(LIB, objs):
+        subprocess.check_call([NVCC, "-shared", "-ccbin", CXX, "-o", LIB] + objs +
+                              ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp", "-Wno-deprecated-gpu-targets"])
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,228 @@
+// C ABI, part 1: Initialize / CreateGeometry / DestroyGeometry and the scene queries.
+// Replaces PW::Tracer::Initialize, CreateGeometry, DestroyGeometry (CUTracer.cu:220-338) and the
+// static scene set-up of GraphicsRTX::DoOnUpdate (GraphicsRTX.cpp:165-167).
+#include <cstring>
+
+#include "context.h"
+#include "obj_loader.h"
+
+namespace mcpt {
+
+Context& ctx() {
+    static Context c;
+    return c;
+}
+
+int fail(int code, const std::string& msg) {
+    ctx().last_error = msg;
+    return code;
+}
+
+int fail_cuda(cudaError_t e, const char* what) {
+    return fail(MCPT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+namespace {
+
+template <class T>
+cudaError_t upload(DeviceBuffer<T>& dst, const std::vector<T>& src, cudaStream_t s) {
+    cudaError_t e = dst.ensure(src.size());
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyAsync(dst.ptr, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice, s);
+}
+
+void release_device_scene(Context& c) {
+    c.d_ref_nodes.release(); c.d_kd_nodes.release(); c.d_leaf_ids.release(); c.d_tri_isect.release();
+    c.d_tri_shade.release(); c.d_mats.release(); c.d_emitters.release();
+    c.uploaded = false;
+}
+
+int install_scene(HostScene&& scene, int build_mode) {
+    Context& c = ctx();
+    std::string err;
+    if (build_mode != MCPT_BUILD_REFERENCE && build_mode != MCPT_BUILD_SAH) return fail(MCPT_ERR_INVALID, "unknown build_mode");
+    if (!validate_scene(scene, err)) return fail(MCPT_ERR_INVALID, err);
+    c.scene = std::move(scene);
+    build_kd_tree(c.scene, build_mode, c.tree);
+    pack_scene(c.scene, c.tree, c.packed);
+    c.has_geometry = true;
+    c.uploaded = false;
+    if (c.has_device) return ensure_uploaded();
+    return MCPT_OK;
+}
+
+}  // namespace
+
+// Host tables -> HBM.  One H2D copy per table on the context stream.
+int ensure_uploaded() {
+    Context& c = ctx();
+    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry: call mcpt_create_geometry / mcpt_load_obj first");
+    if (c.uploaded) return MCPT_OK;
+    cudaError_t e;
+    if ((e = upload(c.d_ref_nodes, c.packed.ref_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload ref_nodes");
+    if ((e = upload(c.d_kd_nodes, c.packed.kd_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload kd_nodes");
+    if ((e = upload(c.d_leaf_ids, c.packed.leaf_ids, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_ids");
+    if ((e = upload(c.d_tri_isect, c.packed.tri_isect, c.stream)) != cudaSuccess) return fail_cuda(e, "upload tri_isect");
+    if ((e = upload(c.d_tri_shade, c.packed.tri_shade, c.stream)) != cudaSuccess) return fail_cuda(e, "upload tri_shade");
+    if ((e = upload(c.d_mats, c.packed.mats, c.stream)) != cudaSuccess) return fail_cuda(e, "upload mats");
+    if ((e = upload(c.d_emitters, c.packed.emitters, c.stream)) != cudaSuccess) return fail_cuda(e, "upload emitters");
+    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "scene upload");
+    DScene& d = c.dscene;
+    d.ref_nodes = c.d_ref_nodes.ptr; d.kd_nodes = c.d_kd_nodes.ptr; d.leaf_ids = c.d_leaf_ids.ptr;
+    d.tri_isect = c.d_tri_isect.ptr; d.tri_shade = c.d_tri_shade.ptr; d.mats = c.d_mats.ptr; d.emitters = c.d_emitters.ptr;
+    for (int i = 0; i < 3; ++i) { d.bmin[i] = c.packed.bmin[i]; d.bmax[i] = c.packed.bmax[i]; }
+    d.num_nodes = static_cast<uint32_t>(c.tree.num_nodes());
+    d.num_tris = static_cast<uint32_t>(c.scene.num_triangles());
+    d.num_mats = static_cast<uint32_t>(c.scene.num_materials());
+    d.num_emitters = c.packed.emitter_area > 0 ? static_cast<uint32_t>(c.packed.emitters.size() / 3) : 0u;
+    d.emitter_area = c.packed.emitter_area;
+    c.uploaded = true;
+    return MCPT_OK;
+}
+
+}  // namespace mcpt
+
+using namespace mcpt;
+
+extern "C" {
+
+int mcpt_initialize(int device) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(MCPT_ERR_NO_DEVICE, std::string("no CUDA device visible (") + (e != cudaSuccess ? cudaGetErrorString(e) : "count = 0") +
+                                            "); libmcpt is GPU-only and has no CPU fallback");
+    }
+    if (device < 0 || device >= n) return fail(MCPT_ERR_INVALID, "device index out of range");
+    if (c.has_device && c.device == device) return MCPT_OK;
+    if (c.has_device) return fail(MCPT_ERR_INVALID, "already initialised on another device; call mcpt_shutdown first");
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail_cuda(e, "cudaSetDevice");
+    if ((e = cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking)) != cudaSuccess) return fail_cuda(e, "cudaStreamCreate");
+    for (auto& ev : c.ev)
+        if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail_cuda(e, "cudaEventCreate");
+    c.has_device = true;
+    c.device = device;
+    if (c.has_geometry) return ensure_uploaded();
+    return MCPT_OK;
+}
+
+int mcpt_shutdown(void) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (c.has_device) {
+        cudaSetDevice(c.device);
+        release_device_scene(c);
+        c.d_slices.release(); c.d_slices_sq.release(); c.d_sum.release(); c.d_sumsq.release(); c.d_rgb.release();
+        c.d_frame_seeds.release(); c.d_counter.release(); c.d_rays.release(); c.d_t.release(); c.d_beta.release();
+        c.d_gamma.release(); c.d_tri.release();
+        for (auto& ev : c.ev) { if (ev) cudaEventDestroy(ev); ev = nullptr; }
+        if (c.stream) cudaStreamDestroy(c.stream);
+        c.stream = nullptr;
+    }
+    c.has_device = false;
+    c.device = -1;
+    c.has_geometry = false;
+    c.scene = HostScene(); c.tree = HostTree(); c.packed = PackedScene();
+    return MCPT_OK;
+}
+
+int mcpt_create_geometry(const mcpt_scene_desc* d) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!d || !d->vertices || !d->triangles || !d->materials || d->num_vertices <= 0 || d->num_triangles <= 0 ||
+        d->num_materials <= 0 || d->num_normals < 0 || (d->num_normals > 0 && !d->normals))
+        return fail(MCPT_ERR_INVALID, "mcpt_create_geometry: null or empty scene table");
+    HostScene s;
+    s.vertices.assign(d->vertices, d->vertices + 3 * static_cast<size_t>(d->num_vertices));
+    if (d->num_normals > 0) s.normals.assign(d->normals, d->normals + 3 * static_cast<size_t>(d->num_normals));
+    s.triangles.assign(d->triangles, d->triangles + 7 * static_cast<size_t>(d->num_triangles));
+    s.materials.assign(d->materials, d->materials + 12 * static_cast<size_t>(d->num_materials));
+    return install_scene(std::move(s), d->build_mode);
+}
+
+int mcpt_load_obj(const char* obj_path, const char* mtl_base, int loader, int build_mode) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!obj_path) return fail(MCPT_ERR_INVALID, "mcpt_load_obj: null path");
+    HostScene s;
+    std::string err;
+    if (!load_obj_scene(obj_path, mtl_base ? mtl_base : "", loader, s, err)) return fail(MCPT_ERR_IO, err);
+    return install_scene(std::move(s), build_mode);
+}
+
+int mcpt_load_scene_file(const char* path, int build_mode) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!path) return fail(MCPT_ERR_INVALID, "mcpt_load_scene_file: null path");
+    HostScene s;
+    std::string err;
+    if (!load_scene_file(path, s, err)) return fail(MCPT_ERR_IO, err);
+    return install_scene(std::move(s), build_mode);
+}
+
+int mcpt_destroy_geometry(void) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (c.has_device) { cudaSetDevice(c.device); release_device_scene(c); }
+    c.has_geometry = false;
+    c.scene = HostScene(); c.tree = HostTree(); c.packed = PackedScene();
+    return MCPT_OK;
+}
+
+int mcpt_get_tree_info(mcpt_tree_info* info) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!info) return fail(MCPT_ERR_INVALID, "null info");
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
+    info->num_nodes = static_cast<int32_t>(c.tree.num_nodes());
+    info->num_leaves = static_cast<int32_t>(c.tree.num_leaves);
+    info->num_leaf_refs = static_cast<int32_t>(c.tree.leaf_ids.size());
+    info->max_depth = static_cast<int32_t>(c.tree.max_depth);
+    info->num_emitter_triangles = c.packed.emitter_area > 0 ? static_cast<int32_t>(c.packed.emitters.size() / 3) : 0;
+    info->build_seconds = c.tree.build_seconds;
+    info->device_bytes = c.packed.bytes();
+    return MCPT_OK;
+}
+
+int mcpt_get_tree(uint32_t* left, uint32_t* right, float* aabb6, uint32_t* split_axis, float* split_value,
+                  uint32_t* leaf_offset, uint32_t* leaf_count, uint32_t* leaf_ids) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
+    const HostTree& t = c.tree;
+    const size_t n = t.num_nodes();
+    if (left) std::memcpy(left, t.left.data(), n * 4);
+    if (right) for (size_t k = 0; k < n; ++k) right[k] = t.split_axis[k] ? t.left[k] + 1u : 0xFFFFFFFFu;
+    if (aabb6) std::memcpy(aabb6, t.aabb.data(), n * 24);
+    if (split_axis) std::memcpy(split_axis, t.split_axis.data(), n * 4);
+    if (split_value) std::memcpy(split_value, t.split_value.data(), n * 4);
+    if (leaf_offset) std::memcpy(leaf_offset, t.leaf_offset.data(), n * 4);
+    if (leaf_count) std::memcpy(leaf_count, t.leaf_count.data(), n * 4);
+    if (leaf_ids) std::memcpy(leaf_ids, t.leaf_ids.data(), t.leaf_ids.size() * 4);
+    return MCPT_OK;
+}
+
+int mcpt_get_scene(int32_t counts[4], float* vertices, float* normals, uint32_t* triangles, float* materials) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
+    const HostScene& s = c.scene;
+    if (counts) {
+        counts[0] = static_cast<int32_t>(s.num_vertices()); counts[1] = static_cast<int32_t>(s.num_normals());
+        counts[2] = static_cast<int32_t>(s.num_triangles()); counts[3] = static_cast<int32_t>(s.num_materials());
+    }
+    if (vertices) std::memcpy(vertices, s.vertices.data(), s.vertices.size() * 4);
+    if (normals) std::memcpy(normals, s.normals.data(), s.normals.size() * 4);
+    if (triangles) std::memcpy(triangles, s.triangles.data(), s.triangles.size() * 4);
+    if (materials) std::memcpy(materials, s.materials.data(), s.materials.size() * 4);
+    return MCPT_OK;
+}
+
+const char* mcpt_last_error(void) { return ctx().last_error.c_str(); }
+const char* mcpt_version(void) { return "mcpt-b200 0.1 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,257 @@
+// C ABI, part 2: RenderScene and the intersection parity hook.
+// Replaces PW::Tracer::RenderScene (CUTracer.cu:340-404) and the per-frame part of
+// GraphicsRTX::DoOnUpdate (GraphicsRTX.cpp:173-209): camera, frame seeds, launch, read-back.
+#include <algorithm>
+#include <cstring>
+#include <random>
+
+#include "context.h"
+#include "launch.h"
+
+using namespace mcpt;
+
+namespace {
+
+// Enough threads to fill 148 SMs several times over; beyond that one thread per pixel keeps all
+// of a pixel's samples in registers.
+int pick_chunks(int width, int height, int spp) {
+    const long long pixels = static_cast<long long>(width) * height;
+    const long long target = 148LL * 2048 * 2;
+    long long chunks = (target + pixels - 1) / pixels;
+    chunks = std::max(1LL, std::min<long long>(chunks, spp));
+    return static_cast<int>(std::min<long long>(chunks, 64));
+}
+
+int check_cfg(const mcpt_render_cfg* cfg) {
+    if (!cfg) return fail(MCPT_ERR_INVALID, "null render cfg");
+    if (cfg->width <= 0 || cfg->height <= 0 || cfg->width > 32768 || cfg->height > 32768) return fail(MCPT_ERR_INVALID, "bad image size");
+    if (cfg->spp <= 0) return fail(MCPT_ERR_INVALID, "spp must be positive");
+    if (cfg->max_depth < 0 || cfg->max_depth > 1000000) return fail(MCPT_ERR_INVALID, "bad max_depth");
+    if (cfg->sample_offset < 0) return fail(MCPT_ERR_INVALID, "negative sample_offset");
+    if (cfg->rng_mode != MCPT_RNG_PHILOX && cfg->rng_mode != MCPT_RNG_REFERENCE) return fail(MCPT_ERR_INVALID, "unknown rng_mode");
+    if (!(cfg->fovy > 0.0f && cfg->fovy < 3.14159f)) return fail(MCPT_ERR_INVALID, "fovy out of range");
+    return MCPT_OK;
+}
+
+// Launches the path-sampling kernel for cfg and leaves per-pixel sums in *sum (and *sumsq).
+// When `dst` is given the samples are ADDED into it (multi-GPU / progressive accumulation),
+// otherwise the result pointer refers to library scratch.
+int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, float4* dstSq, const float4** sum,
+                const float4** sumsq) {
+    Context& c = ctx();
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    if ((rc = ensure_uploaded())) return rc;
+    const bool moments = (cfg->flags & MCPT_FLAG_MOMENTS) != 0;
+    const size_t pixels = static_cast<size_t>(cfg->width) * cfg->height;
+    const int chunks = pick_chunks(cfg->width, cfg->height, cfg->spp);
+    cudaError_t e;
+    if ((e = c.d_slices.ensure(pixels * chunks)) != cudaSuccess) return fail_cuda(e, "alloc slices");
+    if (moments && (e = c.d_slices_sq.ensure(pixels * chunks)) != cudaSuccess) return fail_cuda(e, "alloc slices_sq");
+    if ((e = c.d_counter.ensure(1)) != cudaSuccess) return fail_cuda(e, "alloc counter");
+    if ((e = cudaMemsetAsync(c.d_counter.ptr, 0, sizeof(unsigned long long), stream)) != cudaSuccess) return fail_cuda(e, "memset");
+
+    RenderLaunch r;
+    r.sc = c.dscene;
+    r.cam = make_camera(cfg->eye, cfg->at, cfg->up, cfg->fovy, cfg->width, cfg->height);
+    r.width = cfg->width; r.height = cfg->height;
+    r.sample_begin = cfg->sample_offset; r.sample_count = cfg->spp; r.chunks = chunks;
+    r.depth = static_cast<uint32_t>(cfg->max_depth); r.seed = cfg->seed;
+    r.jitter = (cfg->flags & MCPT_FLAG_NO_JITTER) ? 0u : 1u;
+    r.emission_scale = cfg->emission_scale;
+    r.slices = c.d_slices.ptr;
+    r.slices_sq = moments ? c.d_slices_sq.ptr : nullptr;
+    r.frame_seeds = nullptr;
+    r.ray_counter = c.d_counter.ptr;
+    r.rng_mode = cfg->rng_mode;
+    r.kd = (cfg->flags & MCPT_FLAG_REF_TRAVERSAL) == 0;
+    r.nee = (cfg->flags & MCPT_FLAG_NEE) != 0;
+    r.moments = moments;
+    if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
+        // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))
+        // per frame, i.e. the raw generator output.
+        std::vector<uint32_t> seeds(static_cast<size_t>(cfg->spp));
+        std::mt19937 gen(1234);
+        gen.discard(static_cast<unsigned long long>(cfg->sample_offset));
+        for (auto& s : seeds) s = static_cast<uint32_t>(gen());
+        if ((e = c.d_frame_seeds.ensure(seeds.size())) != cudaSuccess) return fail_cuda(e, "alloc seeds");
+        if ((e = cudaMemcpyAsync(c.d_frame_seeds.ptr, seeds.data(), seeds.size() * 4, cudaMemcpyHostToDevice, stream)) != cudaSuccess)
+            return fail_cuda(e, "upload seeds");
+        if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return fail_cuda(e, "upload seeds");
+        r.frame_seeds = c.d_frame_seeds.ptr;
+    }
+
+    c.counters.launches = 0;
+    cudaEventRecord(c.ev[0], stream);
+    if ((e = launch_render(r, stream, &c.counters.launches)) != cudaSuccess) return fail_cuda(e, "render kernel launch");
+    cudaEventRecord(c.ev[1], stream);
+
+    if (dst) {
+        if ((e = launch_reduce_slices(c.d_slices.ptr, chunks, pixels, dst, true, stream, &c.counters.launches)) != cudaSuccess) return fail_cuda(e, "reduce");
+        if (moments && dstSq &&
+            (e = launch_reduce_slices(c.d_slices_sq.ptr, chunks, pixels, dstSq, true, stream, &c.counters.launches)) != cudaSuccess) return fail_cuda(e, "reduce sq");
+        if (sum) *sum = dst;
+        if (sumsq) *sumsq = dstSq;
+    } else if (chunks > 1) {
+        if ((e = c.d_sum.ensure(pixels)) != cudaSuccess) return fail_cuda(e, "alloc sum");
+        if ((e = launch_reduce_slices(c.d_slices.ptr, chunks, pixels, c.d_sum.ptr, false, stream, &c.counters.launches)) != cudaSuccess) return fail_cuda(e, "reduce");
+        if (moments) {
+            if ((e = c.d_sumsq.ensure(pixels)) != cudaSuccess) return fail_cuda(e, "alloc sumsq");
+            if ((e = launch_reduce_slices(c.d_slices_sq.ptr, chunks, pixels, c.d_sumsq.ptr, false, stream, &c.counters.launches)) != cudaSuccess) return fail_cuda(e, "reduce sq");
+        }
+        if (sum) *sum = c.d_sum.ptr;
+        if (sumsq) *sumsq = moments ? c.d_sumsq.ptr : nullptr;
+    } else {
+        if (sum) *sum = c.d_slices.ptr;
+        if (sumsq) *sumsq = moments ? c.d_slices_sq.ptr : nullptr;
+    }
+    c.counters.paths = static_cast<uint64_t>(pixels) * static_cast<uint64_t>(cfg->spp);
+    return MCPT_OK;
+}
+
+int finish_counters(cudaStream_t stream) {
+    Context& c = ctx();
+    cudaError_t e;
+    unsigned long long rays = 0;
+    if ((e = cudaMemcpyAsync(&rays, c.d_counter.ptr, sizeof(rays), cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return fail_cuda(e, "counter readback");
+    cudaEventRecord(c.ev[2], stream);
+    if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return fail_cuda(e, "render");
+    float k = 0, t = 0;
+    cudaEventElapsedTime(&k, c.ev[0], c.ev[1]);
+    cudaEventElapsedTime(&t, c.ev[0], c.ev[2]);
+    c.counters.rays = rays;
+    c.counters.kernel_ms = k;
+    c.counters.total_ms = t;
+    return MCPT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void mcpt_default_render_cfg(mcpt_render_cfg* cfg, int width, int height, int spp, int max_depth) {
+    if (!cfg) return;
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->width = width; cfg->height = height; cfg->spp = spp; cfg->max_depth = max_depth;
+    cfg->sample_offset = 0; cfg->seed = 0; cfg->rng_mode = MCPT_RNG_PHILOX; cfg->flags = 0;
+    cfg->eye[0] = 0; cfg->eye[1] = 5; cfg->eye[2] = 17;  // GraphicsRTX.cpp:175-177
+    cfg->at[0] = 0; cfg->at[1] = 5; cfg->at[2] = 16;
+    cfg->up[0] = 0; cfg->up[1] = 1; cfg->up[2] = 0;
+    cfg->fovy = 3.141592654f / 4.0f;  // float(D3DX_PI) / 4, GraphicsRTX.cpp:183
+    cfg->emission_scale = 1.0f;
+}
+
+int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m2) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!host_rgb) return fail(MCPT_ERR_INVALID, "null host_rgb");
+    if (host_m2 && !(cfg && (cfg->flags & MCPT_FLAG_MOMENTS))) return fail(MCPT_ERR_INVALID, "host_m2 needs MCPT_FLAG_MOMENTS");
+    const float4 *sum = nullptr, *sumsq = nullptr;
+    int rc = render_core(cfg, c.stream, nullptr, nullptr, &sum, &sumsq);
+    if (rc) return rc;
+    const size_t pixels = static_cast<size_t>(cfg->width) * cfg->height;
+    cudaError_t e;
+    if ((e = c.d_rgb.ensure(3 * pixels)) != cudaSuccess) return fail_cuda(e, "alloc rgb");
+    if ((e = launch_finalize(sum, pixels, c.d_rgb.ptr, c.stream, &c.counters.launches)) != cudaSuccess) return fail_cuda(e, "finalize");
+    if ((e = cudaMemcpyAsync(host_rgb, c.d_rgb.ptr, 3 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H");
+    if (host_m2) {
+        if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "render");
+        if ((e = launch_finalize(sumsq, pixels, c.d_rgb.ptr, c.stream, &c.counters.launches)) != cudaSuccess) return fail_cuda(e, "finalize m2");
+        if ((e = cudaMemcpyAsync(host_m2, c.d_rgb.ptr, 3 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H m2");
+    }
+    return finish_counters(c.stream);
+}
+
+int mcpt_render_accumulate_device(const mcpt_render_cfg* cfg, void* dev_sum, void* dev_sumsq, void* stream) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!dev_sum) return fail(MCPT_ERR_INVALID, "null dev_sum");
+    cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : c.stream;
+    int rc = render_core(cfg, s, static_cast<float4*>(dev_sum), static_cast<float4*>(dev_sumsq), nullptr, nullptr);
+    if (rc) return rc;
+    return finish_counters(s);
+}
+
+int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, void* dev_tri, void* dev_t,
+                                void* dev_beta, void* dev_gamma, void* stream) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (n < 0 || (n > 0 && (!dev_rays || !dev_tri))) return fail(MCPT_ERR_INVALID, "bad ray batch");
+    if (variant != MCPT_ISECT_REFERENCE && variant != MCPT_ISECT_KD) return fail(MCPT_ERR_INVALID, "unknown variant");
+    int rc = ensure_uploaded();
+    if (rc) return rc;
+    cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : c.stream;
+    c.counters.launches = 0;
+    cudaEventRecord(c.ev[0], s);
+    cudaError_t e = launch_intersect(c.dscene, static_cast<const float*>(dev_rays), n, variant, static_cast<int32_t*>(dev_tri),
+                                     static_cast<float*>(dev_t), static_cast<float*>(dev_beta), static_cast<float*>(dev_gamma),
+                                     s, &c.counters.launches);
+    if (e != cudaSuccess) return fail_cuda(e, "intersect launch");
+    cudaEventRecord(c.ev[1], s);
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail_cuda(e, "intersect");
+    float k = 0;
+    cudaEventElapsedTime(&k, c.ev[0], c.ev[1]);
+    c.counters.paths = 0; c.counters.rays = static_cast<uint64_t>(n); c.counters.kernel_ms = k; c.counters.total_ms = k;
+    return MCPT_OK;
+}
+
+int mcpt_intersect_batch(const float* rays, int64_t n, int variant, int32_t* tri, float* t, float* beta, float* gamma) {
+    Context& c = ctx();
+    {
+        std::lock_guard<std::mutex> g(c.lock);
+        if (n < 0 || (n > 0 && (!rays || !tri))) return fail(MCPT_ERR_INVALID, "bad ray batch");
+        int rc = ensure_uploaded();
+        if (rc) return rc;
+        if (n == 0) return MCPT_OK;
+        const size_t N = static_cast<size_t>(n);
+        cudaError_t e;
+        if ((e = c.d_rays.ensure(6 * N)) != cudaSuccess || (e = c.d_tri.ensure(N)) != cudaSuccess || (e = c.d_t.ensure(N)) != cudaSuccess ||
+            (e = c.d_beta.ensure(N)) != cudaSuccess || (e = c.d_gamma.ensure(N)) != cudaSuccess)
+            return fail_cuda(e, "alloc ray batch");
+        if ((e = cudaMemcpyAsync(c.d_rays.ptr, rays, 6 * N * sizeof(float), cudaMemcpyHostToDevice, c.stream)) != cudaSuccess) return fail_cuda(e, "H2D rays");
+    }
+    int rc = mcpt_intersect_batch_device(c.d_rays.ptr, n, variant, c.d_tri.ptr, c.d_t.ptr, c.d_beta.ptr, c.d_gamma.ptr, nullptr);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> g(c.lock);
+    const size_t N = static_cast<size_t>(n);
+    cudaError_t e = cudaMemcpy(tri, c.d_tri.ptr, N * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && t) e = cudaMemcpy(t, c.d_t.ptr, N * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && beta) e = cudaMemcpy(beta, c.d_beta.ptr, N * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && gamma) e = cudaMemcpy(gamma, c.d_gamma.ptr, N * 4, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return fail_cuda(e, "D2H hits");
+    return MCPT_OK;
+}
+
+int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    int rc = check_cfg(cfg);
+    if (rc) return rc;
+    if (!host_rays || sample < 0) return fail(MCPT_ERR_INVALID, "bad arguments");
+    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    const size_t pixels = static_cast<size_t>(cfg->width) * cfg->height;
+    cudaError_t e;
+    if ((e = c.d_rays.ensure(6 * pixels)) != cudaSuccess) return fail_cuda(e, "alloc rays");
+    uint32_t frameSeed = 0;
+    if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
+        std::mt19937 gen(1234);
+        gen.discard(static_cast<unsigned long long>(sample));
+        frameSeed = static_cast<uint32_t>(gen());
+    }
+    DCamera cam = make_camera(cfg->eye, cfg->at, cfg->up, cfg->fovy, cfg->width, cfg->height);
+    c.counters.launches = 0;
+    if ((e = launch_primary_rays(cam, cfg->width, cfg->height, sample, cfg->seed, (cfg->flags & MCPT_FLAG_NO_JITTER) ? 0u : 1u,
+                                 cfg->rng_mode, frameSeed, c.d_rays.ptr, c.stream, &c.counters.launches)) != cudaSuccess)
+        return fail_cuda(e, "primary rays launch");
+    if ((e = cudaMemcpyAsync(host_rays, c.d_rays.ptr, 6 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H rays");
+    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "primary rays");
+    return MCPT_OK;
+}
+
+int mcpt_get_counters(mcpt_counters* out) {
+    if (!out) return fail(MCPT_ERR_INVALID, "null counters");
+    *out = ctx().counters;
+    return MCPT_OK;
+}
+
+}  // extern "C"

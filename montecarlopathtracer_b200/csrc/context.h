@@ -1,0 +1,67 @@
+// Process-global tracer state behind the C ABI (the reference keeps module-level __device__
+// globals, CUTracer.cu:30-42; here it is one struct so that DestroyGeometry really frees).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <mutex>
+#include <string>
+
+#include "../../include/mcpt.h"
+#include "device_scene.h"
+#include "host_scene.h"
+
+namespace mcpt {
+
+template <class T>
+struct DeviceBuffer {
+    T* ptr = nullptr;
+    size_t count = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= count && ptr) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&ptr), (n ? n : 1) * sizeof(T));
+        if (e == cudaSuccess) count = n;
+        return e;
+    }
+    void release() {
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        count = 0;
+    }
+};
+
+struct Context {
+    std::mutex lock;
+    bool has_device = false;
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+    bool has_geometry = false, uploaded = false;
+    HostScene scene;
+    HostTree tree;
+    PackedScene packed;
+    DScene dscene{};
+    DeviceBuffer<float4> d_ref_nodes, d_tri_isect, d_tri_shade, d_mats, d_emitters;
+    DeviceBuffer<uint2> d_kd_nodes;
+    DeviceBuffer<uint32_t> d_leaf_ids;
+
+    // render scratch, grown on demand and kept
+    DeviceBuffer<float4> d_slices, d_slices_sq, d_sum, d_sumsq;
+    DeviceBuffer<float> d_rgb;
+    DeviceBuffer<uint32_t> d_frame_seeds;
+    DeviceBuffer<unsigned long long> d_counter;
+    // intersect scratch
+    DeviceBuffer<float> d_rays, d_t, d_beta, d_gamma;
+    DeviceBuffer<int32_t> d_tri;
+
+    mcpt_counters counters{};
+    std::string last_error;
+};
+
+Context& ctx();
+int fail(int code, const std::string& msg);
+int fail_cuda(cudaError_t e, const char* what);
+int ensure_uploaded();  // needs lock held
+
+}  // namespace mcpt

@@ -1,0 +1,117 @@
+// Packs the host tables + flattened tree into the HBM layout described in device_scene.h.
+// Compiled with -ffp-contract=off: e1, e2 and c3 must round exactly as the reference's
+// per-ray expressions do (rtx.hlsl:167-186 with Math.hpp:169-175's determinant order).
+#include "device_scene.h"
+
+#include <cmath>
+#include <cstring>
+
+namespace mcpt {
+
+namespace {
+inline float as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+inline uint32_t as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+}  // namespace
+
+void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) {
+    const size_t nN = tree.num_nodes(), nT = scene.num_triangles(), nM = scene.num_materials();
+    out.ref_nodes.resize(2 * nN);
+    out.kd_nodes.resize(nN);
+    for (size_t k = 0; k < nN; ++k) {
+        const float* bb = &tree.aabb[6 * k];
+        uint32_t a, b, kx, ky;
+        if (tree.split_axis[k] != 0) {
+            a = tree.left[k];
+            b = 0u;
+            kx = as_uint(tree.split_value[k]);
+            ky = (tree.left[k] << 2) | (tree.split_axis[k] - 1u);
+        } else {
+            a = tree.leaf_offset[k];
+            b = 0x80000000u | tree.leaf_count[k];
+            kx = tree.leaf_offset[k];
+            ky = (tree.leaf_count[k] << 2) | 3u;
+        }
+        out.ref_nodes[2 * k] = make_float4(bb[0], bb[1], bb[2], as_float(a));
+        out.ref_nodes[2 * k + 1] = make_float4(bb[3], bb[4], bb[5], as_float(b));
+        out.kd_nodes[k] = make_uint2(kx, ky);
+    }
+    out.leaf_ids = tree.leaf_ids;
+    if (out.leaf_ids.empty()) out.leaf_ids.push_back(0u);
+    for (int i = 0; i < 3; ++i) { out.bmin[i] = tree.aabb[i]; out.bmax[i] = tree.aabb[3 + i]; }
+
+    out.tri_isect.resize(3 * nT);
+    out.tri_shade.resize(3 * nT);
+    out.emitters.clear();
+    double areaSum = 0.0;
+    std::vector<double> areas;
+    for (size_t t = 0; t < nT; ++t) {
+        const uint32_t* r = &scene.triangles[7 * t];
+        const float* a = &scene.vertices[3 * static_cast<size_t>(r[0])];
+        const float* b = &scene.vertices[3 * static_cast<size_t>(r[1])];
+        const float* c = &scene.vertices[3 * static_cast<size_t>(r[2])];
+        const float e1[3] = {a[0] - b[0], a[1] - b[1], a[2] - b[2]};
+        const float e2[3] = {a[0] - c[0], a[1] - c[1], a[2] - c[2]};
+        const float c3 = e1[1] * e2[2] - e2[1] * e1[2];
+        out.tri_isect[3 * t] = make_float4(a[0], a[1], a[2], c3);
+        out.tri_isect[3 * t + 1] = make_float4(e1[0], e1[1], e1[2], 0.0f);
+        out.tri_isect[3 * t + 2] = make_float4(e2[0], e2[1], e2[2], 0.0f);
+        const float* n0 = &scene.normals[3 * static_cast<size_t>(r[3])];
+        const float* n1 = &scene.normals[3 * static_cast<size_t>(r[4])];
+        const float* n2 = &scene.normals[3 * static_cast<size_t>(r[5])];
+        out.tri_shade[3 * t] = make_float4(n0[0], n0[1], n0[2], as_float(r[6]));
+        out.tri_shade[3 * t + 1] = make_float4(n1[0], n1[1], n1[2], 0.0f);
+        out.tri_shade[3 * t + 2] = make_float4(n2[0], n2[1], n2[2], 0.0f);
+        // Emitter iff any Ka component > 0 (rtx.hlsl:330).
+        const float* Ka = &scene.materials[12 * static_cast<size_t>(r[6])];
+        if (Ka[0] > 0 || Ka[1] > 0 || Ka[2] > 0) {
+            const double u[3] = {double(b[0]) - a[0], double(b[1]) - a[1], double(b[2]) - a[2]};
+            const double v[3] = {double(c[0]) - a[0], double(c[1]) - a[1], double(c[2]) - a[2]};
+            const double cx = u[1] * v[2] - u[2] * v[1], cy = u[2] * v[0] - u[0] * v[2], cz = u[0] * v[1] - u[1] * v[0];
+            const double area = 0.5 * std::sqrt(cx * cx + cy * cy + cz * cz);
+            areas.push_back(area);
+            areaSum += area;
+            out.emitters.push_back(make_float4(a[0], a[1], a[2], static_cast<float>(area)));
+            out.emitters.push_back(make_float4(static_cast<float>(u[0]), static_cast<float>(u[1]), static_cast<float>(u[2]), 0.0f));
+            out.emitters.push_back(make_float4(static_cast<float>(v[0]), static_cast<float>(v[1]), static_cast<float>(v[2]), as_float(static_cast<uint32_t>(t))));
+        }
+    }
+    // running CDF over emitter area for area-uniform light sampling
+    double run = 0.0;
+    for (size_t i = 0; i < areas.size(); ++i) {
+        run += areas[i];
+        out.emitters[3 * i + 1].w = (i + 1 == areas.size()) ? 1.0f : static_cast<float>(run / areaSum);
+    }
+    out.emitter_area = static_cast<float>(areaSum);
+    if (out.emitters.empty()) out.emitters.resize(3, make_float4(0, 0, 0, 0));
+
+    out.mats.resize(3 * nM);
+    for (size_t m = 0; m < nM; ++m) {
+        const float* p = &scene.materials[12 * m];
+        out.mats[3 * m] = make_float4(p[0], p[1], p[2], p[9]);       // Ka, Ns
+        out.mats[3 * m + 1] = make_float4(p[3], p[4], p[5], p[10]);  // Kd, Tr
+        out.mats[3 * m + 2] = make_float4(p[6], p[7], p[8], p[11]);  // Ks, Ni
+    }
+}
+
+// D3DXMatrixLookAtRH / Inverse / PerspectiveFovRH in closed form (GraphicsRTX.cpp:173-184):
+// zaxis = normalize(eye - at), xaxis = normalize(up x zaxis), yaxis = zaxis x xaxis,
+// inverse view rows = xaxis, yaxis, zaxis, eye; _22 = cot(fovy/2), _11 = _22 / (w/h).
+DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height) {
+    DCamera cam;
+    auto norm = [](float v[3]) {
+        float l = sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        v[0] /= l; v[1] /= l; v[2] /= l;
+    };
+    float z[3] = {eye[0] - at[0], eye[1] - at[1], eye[2] - at[2]};
+    norm(z);
+    float x[3] = {up[1] * z[2] - up[2] * z[1], up[2] * z[0] - up[0] * z[2], up[0] * z[1] - up[1] * z[0]};
+    norm(x);
+    float y[3] = {z[1] * x[2] - z[2] * x[1], z[2] * x[0] - z[0] * x[2], z[0] * x[1] - z[1] * x[0]};
+    for (int i = 0; i < 3; ++i) { cam.inv[0][i] = x[i]; cam.inv[1][i] = y[i]; cam.inv[2][i] = z[i]; cam.inv[3][i] = eye[i]; }
+    float aspect = 1.0f * width / height;
+    cam.p22 = static_cast<float>(1.0 / std::tan(static_cast<double>(fovy) * 0.5));
+    cam.p11 = cam.p22 / aspect;
+    return cam;
+}
+
+}  // namespace mcpt

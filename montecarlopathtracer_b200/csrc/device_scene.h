@@ -1,0 +1,67 @@
+// Device-resident scene layout (HBM) and the host routine that packs it.
+//
+// The reference uploads 304-byte CSKDTree nodes with 64 inline triangle ids, 28-byte index
+// triangles and separate float3 vertex/normal buffers (Structure.hpp:196-223), so one triangle
+// test costs three dependent gathers (rtx.hlsl:164-166).  Here everything a traversal step needs
+// is one or two aligned 128-bit loads:
+//
+//   ref_nodes  2 x float4 per node   {lo.xyz, a} {hi.xyz, b}      reference-order AABB traversal
+//                 inner: a = left child index (right = left+1), b = 0
+//                 leaf : a = offset into leaf_ids,             b = 0x80000000 | count
+//   kd_nodes   1 x uint2 per node (8 B)                            plane traversal (render path)
+//                 inner: x = float bits of the split plane, y = (left << 2) | axis(0..2)
+//                 leaf : x = offset into leaf_ids,           y = (count << 2) | 3
+//   leaf_ids   uint32, ascending inside a leaf (the reference's std::set order)
+//   tri_isect  3 x float4 per triangle {a.xyz, c3} {e1.xyz, 0} {e2.xyz, 0}
+//                 e1 = a-b, e2 = a-c (the ray-independent columns of rtx.hlsl:167-186),
+//                 c3 = e1.y*e2.z - e2.y*e1.z (the one ray-independent cofactor)
+//   tri_shade  3 x float4 per triangle {n0.xyz, matId bits} {n1.xyz, 0} {n2.xyz, 0}
+//   mats       3 x float4 per material {Ka, Ns} {Kd, Tr} {Ks, Ni}
+//   emitters   3 x float4 per emitting triangle {a.xyz, area} {b-a, cdf} {c-a, triangle id bits}
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <vector>
+
+#include "host_scene.h"
+
+namespace mcpt {
+
+struct DScene {
+    const float4* ref_nodes;
+    const uint2* kd_nodes;
+    const uint32_t* leaf_ids;
+    const float4* tri_isect;
+    const float4* tri_shade;
+    const float4* mats;
+    const float4* emitters;
+    float bmin[3], bmax[3];
+    uint32_t num_nodes, num_tris, num_mats, num_emitters;
+    float emitter_area;
+};
+
+// rows xaxis, yaxis, zaxis, eye of the inverse view matrix + the two projection scales
+// (GraphicsRTX.cpp:173-184; closed forms in DESIGN.md).
+struct DCamera {
+    float inv[4][3];
+    float p11, p22;
+};
+
+struct PackedScene {
+    std::vector<float4> ref_nodes;
+    std::vector<uint2> kd_nodes;
+    std::vector<uint32_t> leaf_ids;
+    std::vector<float4> tri_isect, tri_shade, mats, emitters;
+    float bmin[3], bmax[3];
+    float emitter_area = 0.0f;
+    size_t bytes() const {
+        return ref_nodes.size() * 16 + kd_nodes.size() * 8 + leaf_ids.size() * 4 +
+               (tri_isect.size() + tri_shade.size() + mats.size() + emitters.size()) * 16;
+    }
+};
+
+void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out);
+DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height);
+
+}  // namespace mcpt

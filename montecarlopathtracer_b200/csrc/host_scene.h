@@ -1,0 +1,48 @@
+// Host-side scene tables and the flattened KD-tree, as plain vectors.
+// Field meaning follows the reference's buffer contract CSTriangle / CSMaterial / CSKDTree
+// (MCRT/QuinEngine/Utils/Structure.hpp:196-223).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace mcpt {
+
+struct HostScene {
+    std::vector<float> vertices;     // 3 per vertex
+    std::vector<float> normals;      // 3 per normal
+    std::vector<uint32_t> triangles; // 7 per triangle: v0 v1 v2 n0 n1 n2 matId
+    std::vector<float> materials;    // 12 per material: Ka Kd Ks Ns Tr Ni
+    size_t num_vertices() const { return vertices.size() / 3; }
+    size_t num_normals() const { return normals.size() / 3; }
+    size_t num_triangles() const { return triangles.size() / 7; }
+    size_t num_materials() const { return materials.size() / 12; }
+    const float* vertex(uint32_t tri, int k) const { return &vertices[3 * static_cast<size_t>(triangles[7 * static_cast<size_t>(tri) + k])]; }
+};
+
+// Flattened tree, node k = k-th node in breadth-first order, children adjacent
+// (right = left + 1), as the reference uploads it (ShaderResource.hpp:128-179).
+struct HostTree {
+    std::vector<uint32_t> left;        // 0xFFFFFFFF for a leaf
+    std::vector<float> aabb;           // 6 per node: min xyz, max xyz (clipped node box)
+    std::vector<uint32_t> split_axis;  // 0 = leaf, 1..3 = x,y,z
+    std::vector<float> split_value;
+    std::vector<uint32_t> leaf_offset; // into leaf_ids
+    std::vector<uint32_t> leaf_count;
+    std::vector<uint32_t> leaf_ids;    // ascending inside a leaf
+    uint32_t max_depth = 0;
+    uint32_t num_leaves = 0;
+    double build_seconds = 0.0;
+    size_t num_nodes() const { return left.size(); }
+};
+
+// kd_build.cpp
+// mode 0: node-for-node the tree of KDTree.hpp:58-287; mode 1: own SAH builder.
+void build_kd_tree(const HostScene& scene, int mode, HostTree& out);
+
+// scene_io.cpp
+bool load_scene_file(const std::string& path, HostScene& out, std::string& err);
+bool save_scene_file(const std::string& path, const HostScene& scene, std::string& err);
+bool validate_scene(const HostScene& scene, std::string& err);
+
+}  // namespace mcpt

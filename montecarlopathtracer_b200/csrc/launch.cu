@@ -1,0 +1,132 @@
+// Kernel instantiations and launch wrappers.  Compile for sm_100a with -fmad=false and WITHOUT
+// -use_fast_math: the intersection-parity gate and the per-sample agreement with the CPU oracle
+// rely on IEEE mul/add/div/sqrt that are not contracted.
+#include "launch.h"
+
+#include "../../include/mcpt.h"
+#include "render.cuh"
+
+namespace mcpt {
+
+namespace {
+
+__global__ void __launch_bounds__(256) intersect_kernel(const DScene sc, const float* __restrict__ rays, int64_t n,
+                                                        int variant, int32_t* __restrict__ tri, float* __restrict__ t,
+                                                        float* __restrict__ beta, float* __restrict__ gamma) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float* r = rays + 6 * i;
+    const float ox = __ldg(r), oy = __ldg(r + 1), oz = __ldg(r + 2), dx = __ldg(r + 3), dy = __ldg(r + 4), dz = __ldg(r + 5);
+    const Hit h = variant == MCPT_ISECT_KD ? intersect_kd(sc, ox, oy, oz, dx, dy, dz)
+                                           : intersect_ref(sc, ox, oy, oz, dx, dy, dz);
+    tri[i] = static_cast<int32_t>(h.tri);
+    if (t) t[i] = h.t;
+    if (beta) beta[i] = h.beta;
+    if (gamma) gamma[i] = h.gamma;
+}
+
+template <class RNG>
+__global__ void __launch_bounds__(256) primary_rays_kernel(const DCamera cam, int width, int height, uint32_t sample,
+                                                           uint32_t seed, uint32_t jitter, uint32_t frameSeed,
+                                                           float* __restrict__ rays) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= static_cast<uint32_t>(width) * static_cast<uint32_t>(height)) return;
+    const uint32_t px = i % static_cast<uint32_t>(width), py = i / static_cast<uint32_t>(width);
+    RNG rng;
+    rng.start(i, seed, sample, frameSeed);
+    float u1 = 0.5f, u2 = 0.5f;
+    if (jitter) { u1 = rng.next(); u2 = rng.next(); }
+    F3 o, d;
+    camera_ray(cam, width, height, px, py, u1, u2, o, d);
+    float* r = rays + 6 * static_cast<size_t>(i);
+    r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = d.x; r[4] = d.y; r[5] = d.z;
+}
+
+__global__ void __launch_bounds__(256) reduce_slices_kernel(const float4* __restrict__ slices, int chunks, size_t pixels,
+                                                            float4* __restrict__ dst, int accumulate) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= pixels) return;
+    float4 a = accumulate ? dst[i] : make_float4(0, 0, 0, 0);
+    for (int c = 0; c < chunks; ++c) {
+        const float4 v = slices[static_cast<size_t>(c) * pixels + i];
+        a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+    dst[i] = a;
+}
+
+__global__ void __launch_bounds__(256) finalize_kernel(const float4* __restrict__ sum, size_t pixels, float* __restrict__ rgb) {
+    const size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= pixels) return;
+    const float4 v = sum[i];
+    const float inv = v.w > 0 ? 1.0f / v.w : 0.0f;
+    rgb[3 * i] = v.x * inv; rgb[3 * i + 1] = v.y * inv; rgb[3 * i + 2] = v.z * inv;
+}
+
+template <class RNG, bool KD, bool NEE, bool MOMENTS>
+cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
+    RenderParams p;
+    p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
+    p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
+    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale;
+    p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
+    dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
+    render_kernel<RNG, KD, NEE, MOMENTS><<<grid, 256, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+template <class RNG>
+cudaError_t launch_render_rng(const RenderLaunch& r, cudaStream_t s) {
+    const int key = (r.kd ? 4 : 0) | (r.nee ? 2 : 0) | (r.moments ? 1 : 0);
+    switch (key) {
+        case 0: return launch_render_t<RNG, false, false, false>(r, s);
+        case 1: return launch_render_t<RNG, false, false, true>(r, s);
+        case 2: return launch_render_t<RNG, false, true, false>(r, s);
+        case 3: return launch_render_t<RNG, false, true, true>(r, s);
+        case 4: return launch_render_t<RNG, true, false, false>(r, s);
+        case 5: return launch_render_t<RNG, true, false, true>(r, s);
+        case 6: return launch_render_t<RNG, true, true, false>(r, s);
+        default: return launch_render_t<RNG, true, true, true>(r, s);
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_render(const RenderLaunch& r, cudaStream_t stream, uint32_t* launches) {
+    if (launches) ++*launches;
+    if (r.rng_mode == MCPT_RNG_REFERENCE) return launch_render_rng<RngReference>(r, stream);
+    return launch_render_rng<RngPhilox>(r, stream);
+}
+
+cudaError_t launch_reduce_slices(const float4* slices, int chunks, size_t pixels, float4* dst, bool accumulate,
+                                 cudaStream_t stream, uint32_t* launches) {
+    if (launches) ++*launches;
+    reduce_slices_kernel<<<static_cast<unsigned>((pixels + 255) / 256), 256, 0, stream>>>(slices, chunks, pixels, dst, accumulate ? 1 : 0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_finalize(const float4* sum, size_t pixels, float* rgb, cudaStream_t stream, uint32_t* launches) {
+    if (launches) ++*launches;
+    finalize_kernel<<<static_cast<unsigned>((pixels + 255) / 256), 256, 0, stream>>>(sum, pixels, rgb);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int variant, int32_t* tri, float* t,
+                             float* beta, float* gamma, cudaStream_t stream, uint32_t* launches) {
+    if (n <= 0) return cudaSuccess;
+    if (launches) ++*launches;
+    intersect_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(sc, rays, n, variant, tri, t, beta, gamma);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_primary_rays(const DCamera& cam, int width, int height, int sample, uint32_t seed, uint32_t jitter,
+                                int rng_mode, uint32_t frame_seed, float* rays, cudaStream_t stream, uint32_t* launches) {
+    if (launches) ++*launches;
+    const unsigned blocks = (static_cast<unsigned>(width) * static_cast<unsigned>(height) + 255u) / 256u;
+    if (rng_mode == MCPT_RNG_REFERENCE)
+        primary_rays_kernel<RngReference><<<blocks, 256, 0, stream>>>(cam, width, height, sample, seed, jitter, frame_seed, rays);
+    else
+        primary_rays_kernel<RngPhilox><<<blocks, 256, 0, stream>>>(cam, width, height, sample, seed, jitter, frame_seed, rays);
+    return cudaGetLastError();
+}
+
+}  // namespace mcpt

@@ -1,0 +1,42 @@
+// Host-callable launchers of the sm_100a kernels (launch.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "device_scene.h"
+
+namespace mcpt {
+
+struct RenderLaunch {
+    DScene sc;
+    DCamera cam;
+    int width, height;
+    int sample_begin, sample_count, chunks;
+    uint32_t depth, seed, jitter;
+    float emission_scale;
+    float4* slices;        // [chunks][h][w] scratch (or the destination itself when chunks == 1 and !accumulate)
+    float4* slices_sq;     // nullptr unless moments
+    const uint32_t* frame_seeds;
+    unsigned long long* ray_counter;
+    int rng_mode;          // MCPT_RNG_*
+    bool kd, nee, moments;
+};
+
+// Number of kernels launched is returned through *launches (adds to it).
+cudaError_t launch_render(const RenderLaunch& r, cudaStream_t stream, uint32_t* launches);
+
+// dst[i] (+)= sum over chunks of slices[c][i]   (fixed order -> deterministic)
+cudaError_t launch_reduce_slices(const float4* slices, int chunks, size_t pixels, float4* dst, bool accumulate,
+                                 cudaStream_t stream, uint32_t* launches);
+
+// rgb[i*3..] = sum[i].xyz / sum[i].w
+cudaError_t launch_finalize(const float4* sum, size_t pixels, float* rgb, cudaStream_t stream, uint32_t* launches);
+
+cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int variant, int32_t* tri, float* t,
+                             float* beta, float* gamma, cudaStream_t stream, uint32_t* launches);
+
+cudaError_t launch_primary_rays(const DCamera& cam, int width, int height, int sample, uint32_t seed, uint32_t jitter,
+                                int rng_mode, uint32_t frame_seed, float* rays, cudaStream_t stream, uint32_t* launches);
+
+}  // namespace mcpt

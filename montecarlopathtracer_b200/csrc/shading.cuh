@@ -1,0 +1,156 @@
+// Random streams and BSDF direction samplers (device).
+//
+// Samplers follow rtx.hlsl:213-302 statement by statement (same special cases, same operand
+// order); this translation unit is compiled with -fmad=false and without fast-math so the only
+// differences from the CPU oracle are libm-vs-CUDA ulps in pow/sin/cos.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+namespace mcpt {
+
+struct F3 {
+    float x, y, z;
+};
+__device__ __forceinline__ F3 f3(float x, float y, float z) { return {x, y, z}; }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ F3 operator-(F3 a, F3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ F3 operator*(F3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
+__device__ __forceinline__ F3 operator*(F3 a, F3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
+__device__ __forceinline__ F3 operator/(F3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+__device__ __forceinline__ F3 operator-(F3 a) { return {-a.x, -a.y, -a.z}; }
+__device__ __forceinline__ float dot(F3 a, F3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ F3 normalize(F3 v) { return v * (1.0f / sqrtf(dot(v, v))); }
+
+// ---- Philox4x32-10 (Salmon et al. 2011), counter-based: key = (pixel, seed),
+// counter = (sample, slot, block, 0); slot 0 = camera jitter, slot b+1 = scattering event b,
+// slot 0x80000000|(b+1) = next-event estimation at event b.  u = ((x >> 8) + 1) * 2^-24 in (0,1].
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+struct RngPhilox {
+    uint32_t k0, k1, sample, slot, draw;
+    uint32_t b0, b1, b2, b3;
+    __device__ __forceinline__ void start(uint32_t pixel, uint32_t seed, uint32_t sampleIndex, uint32_t /*frameSeed*/) {
+        k0 = pixel; k1 = seed; sample = sampleIndex; slot = 0; draw = 0;
+    }
+    __device__ __forceinline__ void set_slot(uint32_t s) { slot = s; draw = 0; }
+    __device__ __forceinline__ float next() {
+        if ((draw & 3u) == 0u) {
+            uint32_t o[4];
+            philox4x32_10(sample, slot, draw >> 2, 0u, k0, k1, o);
+            b0 = o[0]; b1 = o[1]; b2 = o[2]; b3 = o[3];
+        }
+        const uint32_t i = draw & 3u;
+        const uint32_t x = i == 0 ? b0 : (i == 1 ? b1 : (i == 2 ? b2 : b3));
+        ++draw;
+        return static_cast<float>((x >> 8) + 1u) * (1.0f / 16777216.0f);
+    }
+};
+
+// ---- the reference stream: rtx.hlsl:61-72 (TEA, 16 rounds) and :74-82 (Park-Miller via
+// Schrage in uint arithmetic), seeded per (pixel, frame) and warmed by two draws (:380-382).
+struct RngReference {
+    uint32_t sd;
+    __device__ __forceinline__ void start(uint32_t pixel, uint32_t /*seed*/, uint32_t /*sampleIndex*/, uint32_t frameSeed) {
+        uint32_t v0 = pixel, v1 = frameSeed, sum = 0;
+#pragma unroll
+        for (int n = 0; n < 16; ++n) {
+            sum += 0x9e3779b9u;
+            v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + sum) ^ ((v1 >> 5) + 0xc8013ea4u);
+            v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + sum) ^ ((v0 >> 5) + 0x7e95761eu);
+        }
+        sd = v0;
+        next();
+        next();
+    }
+    __device__ __forceinline__ void set_slot(uint32_t) {}
+    __device__ __forceinline__ float next() {
+        sd = 16807u * (sd % 127773u) - 2836u * (sd / 127773u);
+        if (sd > 0x7FFFFFFFu) sd += 0x7FFFFFFFu;
+        return __fdiv_rn(__uint2float_rn(sd), 2147483648.0f);
+    }
+};
+
+#define MCPT_PI 3.14159265358979323846f
+#define MCPT_EPS 1.192092896e-07f
+
+// rtx.hlsl:213-251
+template <class RNG>
+__device__ __forceinline__ F3 sample_fresnel(RNG& rng, F3 normal, F3 dir, float Tr, float Ni) {
+    const float x = rng.next();
+    F3 outdir;
+    const float ndoti = dot(dir, normal);
+    Tr = Tr * (1 - powf(1 - fabsf(ndoti), 5.0f));
+    if (x < Tr) {
+        if (ndoti <= 0) {
+            const float alpha = -ndoti / Ni - sqrtf(1 - (1 - ndoti * ndoti) / Ni / Ni);
+            outdir = normal * alpha + dir / Ni;
+        } else {
+            const float test = 1 - (1 - ndoti * ndoti) * Ni * Ni;
+            if (test < 0) {
+                outdir = dir - normal * dot(dir, normal) * 2;
+            } else {
+                const float alpha = -ndoti * Ni + sqrtf(test);
+                outdir = normal * alpha + dir * Ni;
+            }
+        }
+    } else {
+        outdir = dir - normal * dot(dir, normal) * 2;
+    }
+    return normalize(outdir);
+}
+
+// Rotation of a +Y-centred lobe direction onto `normal` (rtx.hlsl:262-274 / :287-300).
+// divideByInvlen selects samplePhong's `d.z / invlen` against sampleHemi's `d.z * (1/invlen)`.
+__device__ __forceinline__ F3 rotate_to(F3 d, F3 normal, bool divideByInvlen) {
+    if (fabsf(normal.y + 1) < MCPT_EPS) return -d;
+    if (fabsf(normal.y - 1) >= MCPT_EPS) {
+        const float invlen = 1.0f / sqrtf(1.0f - normal.y * normal.y);
+        F3 o;
+        o.x = (normal.z * d.x + normal.x * normal.y * d.z) * invlen + normal.x * d.y;
+        o.y = divideByInvlen ? (normal.y * d.y - d.z / invlen) : (normal.y * d.y - d.z * (1.0f / invlen));
+        o.z = (-normal.x * d.x + normal.z * normal.y * d.z) * invlen + normal.z * d.y;
+        return o;
+    }
+    return d;
+}
+
+// rtx.hlsl:253-276
+template <class RNG>
+__device__ __forceinline__ F3 sample_phong(RNG& rng, F3 normal, F3 dir, float Ns) {
+    const float x = rng.next();
+    const float y = rng.next();
+    const float cosT = powf(x, 1.0f / (Ns + 1));
+    const float sinT = sqrtf(1 - cosT * cosT);
+    const float phi = 2 * MCPT_PI * y;
+    float s, c;
+    sincosf(phi, &s, &c);
+    const F3 halfdir = rotate_to(f3(sinT * c, cosT, sinT * s), normal, true);
+    return dir - halfdir * dot(dir, halfdir) * 2;
+}
+
+// rtx.hlsl:278-302
+template <class RNG>
+__device__ __forceinline__ F3 sample_hemi(RNG& rng, F3 normal) {
+    const float x = rng.next();
+    const float y = rng.next();
+    const float sinT = sqrtf(x);
+    const float cosT = sqrtf(1 - x);
+    const float phi = 2 * MCPT_PI * y;
+    float s, c;
+    sincosf(phi, &s, &c);
+    return rotate_to(f3(sinT * c, cosT, sinT * s), normal, false);
+}
+
+}  // namespace mcpt

@@ -1,0 +1,242 @@
+"""Host-side mirror of the reference's tracer interface over libmcpt.so's C ABI.
+
+The reference exposes the hot path as ``PW::Tracer::{Initialize, CreateGeometry, DestroyGeometry,
+RenderScene}`` (CVMCTracer/CVMCTracer/CUDA/CUTracer.h:9-12); the functions below keep those names
+(snake-cased), argument meaning and call order (``main.cpp:16-18``: read scene -> create geometry
+-> render).  Everything is a thin ctypes call into ``include/mcpt.h``; there is NO CPU fallback:
+if the CUDA library is missing or no GPU is visible the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libmcpt.so")
+
+# enums of include/mcpt.h
+BUILD_REFERENCE, BUILD_SAH = 0, 1
+LOADER_TINYOBJ, LOADER_OBJREADER = 0, 1
+RNG_PHILOX, RNG_REFERENCE = 0, 1
+FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL = 1, 2, 4, 8
+ISECT_REFERENCE, ISECT_KD = 0, 1
+ERR_NO_DEVICE = 4
+
+_vp = C.c_void_p
+
+
+class McptError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"libmcpt error {code}: {msg}")
+        self.code = code
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("vertices", _vp), ("num_vertices", C.c_int32), ("normals", _vp), ("num_normals", C.c_int32),
+                ("triangles", _vp), ("num_triangles", C.c_int32), ("materials", _vp), ("num_materials", C.c_int32),
+                ("build_mode", C.c_int32)]
+
+
+class RenderCfg(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("max_depth", C.c_int32),
+                ("sample_offset", C.c_int32), ("seed", C.c_uint32), ("rng_mode", C.c_int32), ("flags", C.c_uint32),
+                ("eye", C.c_float * 3), ("at", C.c_float * 3), ("up", C.c_float * 3), ("fovy", C.c_float),
+                ("emission_scale", C.c_float)]
+
+
+class Counters(C.Structure):
+    _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("kernel_ms", C.c_double), ("total_ms", C.c_double),
+                ("launches", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class TreeInfo(C.Structure):
+    _fields_ = [("num_nodes", C.c_int32), ("num_leaves", C.c_int32), ("num_leaf_refs", C.c_int32),
+                ("max_depth", C.c_int32), ("num_emitter_triangles", C.c_int32), ("build_seconds", C.c_double),
+                ("device_bytes", C.c_uint64)]
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads libmcpt.so; raises if it has not been built (``python -m montecarlopathtracer_b200.build``)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FileNotFoundError(f"{LIB_PATH} is missing: build it with `python -m montecarlopathtracer_b200.build` "
+                                "(the tracer is CUDA-only, there is no CPU path)")
+    L = C.CDLL(LIB_PATH)
+    L.mcpt_initialize.argtypes = [C.c_int]
+    L.mcpt_create_geometry.argtypes = [C.POINTER(SceneDesc)]
+    L.mcpt_load_obj.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
+    L.mcpt_load_scene_file.argtypes = [C.c_char_p, C.c_int]
+    L.mcpt_get_tree_info.argtypes = [C.POINTER(TreeInfo)]
+    L.mcpt_get_tree.argtypes = [_vp] * 8
+    L.mcpt_get_scene.argtypes = [_vp] * 5
+    L.mcpt_default_render_cfg.argtypes = [C.POINTER(RenderCfg), C.c_int, C.c_int, C.c_int, C.c_int]
+    L.mcpt_default_render_cfg.restype = None
+    L.mcpt_render_scene.argtypes = [C.POINTER(RenderCfg), _vp, _vp]
+    L.mcpt_render_accumulate_device.argtypes = [C.POINTER(RenderCfg), _vp, _vp, _vp]
+    L.mcpt_intersect_batch.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp]
+    L.mcpt_intersect_batch_device.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp]
+    L.mcpt_primary_rays.argtypes = [C.POINTER(RenderCfg), C.c_int, _vp]
+    L.mcpt_get_counters.argtypes = [C.POINTER(Counters)]
+    L.mcpt_last_error.restype = C.c_char_p
+    L.mcpt_version.restype = C.c_char_p
+    _lib = L
+    return L
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise McptError(rc, lib().mcpt_last_error().decode(errors="replace"))
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(_vp)
+
+
+# ---- PW::Tracer::Initialize ---------------------------------------------------------------
+def initialize(device: int = 0) -> None:
+    _check(lib().mcpt_initialize(device))
+
+
+def shutdown() -> None:
+    _check(lib().mcpt_shutdown())
+
+
+# ---- PW::Tracer::CreateGeometry ------------------------------------------------------------
+def create_geometry(vertices, normals, triangles, materials, build_mode: int = BUILD_REFERENCE) -> None:
+    """Flat tables: vertices (V,3) f32, normals (N,3) f32, triangles (T,7) u32 {v0 v1 v2 n0 n1 n2 mat},
+    materials (M,12) f32 {Ka Kd Ks Ns Tr Ni} -- the fields of CSTriangle / CSMaterial."""
+    v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+    n = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+    t = np.ascontiguousarray(triangles, np.uint32).reshape(-1, 7)
+    m = np.ascontiguousarray(materials, np.float32).reshape(-1, 12)
+    d = SceneDesc(_p(v), len(v), _p(n), len(n), _p(t), len(t), _p(m), len(m), build_mode)
+    _check(lib().mcpt_create_geometry(C.byref(d)))
+
+
+def load_obj(obj_path: str, mtl_base: str | None = None, loader: int = LOADER_TINYOBJ,
+             build_mode: int = BUILD_REFERENCE) -> None:
+    if mtl_base is None:
+        mtl_base = os.path.dirname(obj_path) + "/"
+    _check(lib().mcpt_load_obj(obj_path.encode(), mtl_base.encode(), loader, build_mode))
+
+
+def load_scene_file(path: str, build_mode: int = BUILD_REFERENCE) -> None:
+    _check(lib().mcpt_load_scene_file(path.encode(), build_mode))
+
+
+def destroy_geometry() -> None:
+    _check(lib().mcpt_destroy_geometry())
+
+
+def tree_info() -> TreeInfo:
+    info = TreeInfo()
+    _check(lib().mcpt_get_tree_info(C.byref(info)))
+    return info
+
+
+@dataclass
+class Tree:
+    left: np.ndarray
+    right: np.ndarray
+    aabb: np.ndarray
+    split_axis: np.ndarray
+    split_value: np.ndarray
+    leaf_offset: np.ndarray
+    leaf_count: np.ndarray
+    leaf_ids: np.ndarray
+
+
+def get_tree() -> Tree:
+    """The built tree in the reference's BFS layout (ShaderResource.hpp:128-179)."""
+    info = tree_info()
+    n, r = info.num_nodes, max(info.num_leaf_refs, 1)
+    t = Tree(np.empty(n, np.uint32), np.empty(n, np.uint32), np.empty((n, 6), np.float32), np.empty(n, np.uint32),
+             np.empty(n, np.float32), np.empty(n, np.uint32), np.empty(n, np.uint32), np.empty(r, np.uint32))
+    _check(lib().mcpt_get_tree(_p(t.left), _p(t.right), _p(t.aabb), _p(t.split_axis), _p(t.split_value),
+                               _p(t.leaf_offset), _p(t.leaf_count), _p(t.leaf_ids)))
+    t.leaf_ids = t.leaf_ids[:info.num_leaf_refs]
+    return t
+
+
+def get_scene():
+    """-> (vertices, normals, triangles, materials) as loaded."""
+    cnt = (C.c_int32 * 4)()
+    _check(lib().mcpt_get_scene(cnt, None, None, None, None))
+    v = np.empty((cnt[0], 3), np.float32)
+    n = np.empty((cnt[1], 3), np.float32)
+    t = np.empty((cnt[2], 7), np.uint32)
+    m = np.empty((cnt[3], 12), np.float32)
+    _check(lib().mcpt_get_scene(cnt, _p(v), _p(n), _p(t), _p(m)))
+    return v, n, t, m
+
+
+# ---- PW::Tracer::RenderScene ---------------------------------------------------------------
+def render_cfg(width: int, height: int, spp: int, max_depth: int, **kw) -> RenderCfg:
+    cfg = RenderCfg()
+    lib().mcpt_default_render_cfg(C.byref(cfg), width, height, spp, max_depth)
+    for k, v in kw.items():
+        if k in ("eye", "at", "up"):
+            getattr(cfg, k)[:] = list(v)
+        else:
+            setattr(cfg, k, v)
+    return cfg
+
+
+def render_scene(cfg: RenderCfg, out: np.ndarray | None = None, moments: bool = False):
+    """-> hostcolor (H,W,3) float32 linear mean radiance, top row first (and E[x^2] if moments)."""
+    if out is None:
+        out = np.empty((cfg.height, cfg.width, 3), np.float32)
+    m2 = None
+    if moments:
+        cfg.flags |= FLAG_MOMENTS
+        m2 = np.empty((cfg.height, cfg.width, 3), np.float32)
+    _check(lib().mcpt_render_scene(C.byref(cfg), _p(out), _p(m2)))
+    return (out, m2) if moments else out
+
+
+def render_accumulate_device(cfg: RenderCfg, dev_sum_ptr: int, dev_sumsq_ptr: int = 0, stream: int = 0) -> None:
+    """Adds cfg.spp samples into a caller-owned device float4 buffer (e.g. a torch tensor's data_ptr())."""
+    _check(lib().mcpt_render_accumulate_device(C.byref(cfg), _vp(dev_sum_ptr), _vp(dev_sumsq_ptr or None),
+                                               _vp(stream or None)))
+
+
+def intersect_batch(rays: np.ndarray, variant: int = ISECT_REFERENCE):
+    """rays (n,6) -> (tri int32 [-1 = miss], t, beta, gamma)."""
+    rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+    n = len(rays)
+    tri = np.empty(n, np.int32)
+    t = np.empty(n, np.float32)
+    b = np.empty(n, np.float32)
+    g = np.empty(n, np.float32)
+    _check(lib().mcpt_intersect_batch(_p(rays), n, variant, _p(tri), _p(t), _p(b), _p(g)))
+    return tri, t, b, g
+
+
+def intersect_batch_device(rays_ptr: int, n: int, variant: int, tri_ptr: int, t_ptr: int = 0, beta_ptr: int = 0,
+                           gamma_ptr: int = 0, stream: int = 0) -> None:
+    _check(lib().mcpt_intersect_batch_device(_vp(rays_ptr), n, variant, _vp(tri_ptr), _vp(t_ptr or None),
+                                             _vp(beta_ptr or None), _vp(gamma_ptr or None), _vp(stream or None)))
+
+
+def primary_rays(cfg: RenderCfg, sample: int = 0) -> np.ndarray:
+    rays = np.empty((cfg.height * cfg.width, 6), np.float32)
+    _check(lib().mcpt_primary_rays(C.byref(cfg), sample, _p(rays)))
+    return rays
+
+
+def counters() -> Counters:
+    c = Counters()
+    _check(lib().mcpt_get_counters(C.byref(c)))
+    return c
+
+
+def version() -> str:
+    return lib().mcpt_version().decode()

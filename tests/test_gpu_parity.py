@@ -1,0 +1,208 @@
+"""GPU parity tests proper: libmcpt.so (through its C ABI) against the CPU oracle on the same inputs.
+
+Gates (BASELINE.json north_star):
+  * intersection -- triangle ids equal and t / beta / gamma BIT-equal on the fixed ray batch
+    (512x512 un-jittered camera rays + random rays inside the scene box);
+  * image -- mean relative error < 1 % against the oracle render at matched spp and no pixel beyond
+    4 sigma of its sample variance; with the shared Philox stream the two renders are in fact the
+    same paths, so most pixels agree to float rounding.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SCENE_CAMERA = {"scene01": (0, 5, 17), "scene01_lambert": (0, 5, 17), "scene02": (0, 5, 23), "scene03": (0, 5, 17)}
+
+
+def _load(T, s, mode=None):
+    T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_REFERENCE if mode is None else mode)
+
+
+def _random_rays(s, n, seed=1):
+    g = np.random.Generator(np.random.Philox(seed))
+    lo, hi = s.verts.min(0), s.verts.max(0)
+    o = g.uniform(lo, hi, (n, 3))
+    d = g.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return np.concatenate([o, d], 1).astype(np.float32)
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+@pytest.mark.parametrize("rng_mode,jitter", [(0, 0), (0, 1), (1, 1)])
+def test_primary_rays_bit_equal(gpu, oracle, scenes, rng_mode, jitter):
+    """rtx.hlsl:376-398: same pixel -> same ray, bit for bit, in both random streams."""
+    T = gpu
+    _load(T, scenes["scene01"])
+    # oracle rng_mode: 0 = reference stream, 1 = Philox;  library: RNG_PHILOX = 0, RNG_REFERENCE = 1
+    ocfg = oracle.cfg(96, 64, 1, 5, rng_mode=1 - rng_mode, seed=77, jitter=jitter)
+    gcfg = T.render_cfg(96, 64, 1, 5, rng_mode=rng_mode, seed=77, flags=0 if jitter else T.FLAG_NO_JITTER)
+    for sample in (0, 3):
+        assert np.array_equal(_bits(T.primary_rays(gcfg, sample)), _bits(oracle.primary_rays(ocfg, sample)))
+
+
+@pytest.mark.parametrize("name", ["scene01", "scene02", "scene03"])
+def test_intersection_bit_exact_reference_traversal(gpu, oracle, scenes, name):
+    T, s = gpu, scenes[name]
+    _load(T, s)
+    osc = oracle.scene(s)
+    cam = oracle.cfg(512, 512, 1, 5, jitter=0, eye=SCENE_CAMERA[name], at=(0, 5, SCENE_CAMERA[name][2] - 1))
+    for rays in (oracle.primary_rays(cam), _random_rays(s, 1 << 20 if name == "scene01" else 1 << 18)):
+        tri, t, b, g, cnt = osc.intersect(rays)
+        gtri, gt, gb, gg = T.intersect_batch(rays, T.ISECT_REFERENCE)
+        assert np.array_equal(tri, gtri)
+        hit = tri >= 0
+        assert hit.sum() > 0.3 * len(rays)
+        assert np.array_equal(_bits(t)[hit], _bits(gt)[hit])
+        assert np.array_equal(_bits(b)[hit], _bits(gb)[hit])
+        assert np.array_equal(_bits(g)[hit], _bits(gg)[hit])
+
+
+@pytest.mark.parametrize("name", ["scene01", "scene02", "scene03"])
+def test_intersection_kd_traversal_equals_reference(gpu, oracle, scenes, name):
+    """The render path's front-to-back plane traversal returns the same closest hit (same id, same bits):
+    the fixed batch is tie-free, so visit order cannot matter."""
+    T, s = gpu, scenes[name]
+    _load(T, s)
+    osc = oracle.scene(s)
+    cam = oracle.cfg(512, 512, 1, 5, jitter=0, eye=SCENE_CAMERA[name], at=(0, 5, SCENE_CAMERA[name][2] - 1))
+    for rays in (oracle.primary_rays(cam), _random_rays(s, 1 << 18, seed=2)):
+        tri, t, b, g, _ = osc.intersect(rays)
+        ktri, kt, kb, kg = T.intersect_batch(rays, T.ISECT_KD)
+        bad = np.flatnonzero(tri != ktri)
+        assert len(bad) == 0, f"{len(bad)} of {len(rays)} rays differ, first {bad[:5]}"
+        hit = tri >= 0
+        assert np.array_equal(_bits(t)[hit], _bits(kt)[hit]) and np.array_equal(_bits(b)[hit], _bits(kb)[hit])
+
+
+def test_intersection_edge_cases(gpu, oracle, scenes):
+    """Axis-parallel rays (1/0 in the slab test, rtx.hlsl:87-100), rays starting on geometry, rays that
+    leave through the open front, zero-length batches."""
+    T, s = gpu, scenes["scene01"]
+    _load(T, s)
+    osc = oracle.scene(s)
+    rays = []
+    for o in ([0, 5, 16], [0, 0, 0], [-5.76397, 5, 0], [0, 10, 0], [1, 9.9, 0.5], [0, 5, 30]):
+        for d in ([1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1], [0.6, 0.8, 0], [0, -0.6, -0.8]):
+            rays.append(o + d)
+    rays = np.array(rays, np.float32)
+    tri, t, b, g, _ = osc.intersect(rays)
+    for variant in (T.ISECT_REFERENCE, T.ISECT_KD):
+        gtri, gt, gb, gg = T.intersect_batch(rays, variant)
+        assert np.array_equal(tri, gtri), variant
+        assert np.array_equal(_bits(t)[tri >= 0], _bits(gt)[tri >= 0])
+    e = T.intersect_batch(np.zeros((0, 6), np.float32))
+    assert len(e[0]) == 0
+
+
+def _gate(gpu_mean, gpu_m2, o_sum, o_sq, spp):
+    """mean relative error < 1 % and no pixel beyond 4 sigma, sigma^2 = (var_o + var_g)/spp."""
+    o_mean = o_sum / spp
+    rel = abs(gpu_mean.astype(np.float64).mean() - o_mean.mean()) / o_mean.mean()
+    var_o = np.maximum(o_sq / spp - o_mean ** 2, 0)
+    var_g = np.maximum(gpu_m2.astype(np.float64) - gpu_mean.astype(np.float64) ** 2, 0)
+    sigma = np.sqrt((var_o + var_g) / spp) + 1e-4
+    z = np.abs(gpu_mean - o_mean) / sigma
+    return rel, z
+
+
+@pytest.mark.parametrize("name,depth", [("scene01", 5), ("scene01_lambert", 8), ("scene02", 5), ("scene03", 5)])
+def test_render_same_paths_as_oracle_philox(gpu, oracle, scenes, name, depth):
+    """Shared Philox stream: GPU and oracle trace the same paths, so pixels agree to rounding except
+    where a libm-vs-CUDA ulp flips a discrete decision."""
+    T, s = gpu, scenes[name]
+    _load(T, s)
+    eye = SCENE_CAMERA[name]
+    W, H, spp = 96, 96, 8
+    ocfg = oracle.cfg(W, H, spp, depth, rng_mode=1, seed=5, eye=eye, at=(0, 5, eye[2] - 1))
+    osum, osq, _, ocnt = oracle.scene(s).render(ocfg)
+    gcfg = T.render_cfg(W, H, spp, depth, seed=5, eye=eye, at=(0, 5, eye[2] - 1))
+    mean, m2 = T.render_scene(gcfg, moments=True)
+    c = T.counters()
+    assert c.paths == W * H * spp == ocnt.paths
+    assert abs(int(c.rays) - int(ocnt.rays)) <= 0.002 * ocnt.rays
+    close = np.isclose(mean, osum / spp, rtol=1e-3, atol=1e-5).all(-1)
+    assert close.mean() > 0.97, close.mean()
+    rel, z = _gate(mean, m2, osum, osq, spp)
+    assert rel < 0.01
+
+
+def test_render_reference_stream_reproduces_the_reference_estimator(gpu, oracle, scenes):
+    """TEA + LCG with the mt19937(1234) frame seeds: the GPU render IS the reference's render,
+    sample for sample (rtx.hlsl:61-82,380-386; GraphicsRTX.cpp:170-171,192)."""
+    T, s = gpu, scenes["scene01"]
+    _load(T, s)
+    W, H, spp = 64, 64, 6
+    osum, osq, _, ocnt = oracle.scene(s).render(oracle.cfg(W, H, spp, 5))
+    for flags in (0, T.FLAG_REF_TRAVERSAL):
+        mean = T.render_scene(T.render_cfg(W, H, spp, 5, rng_mode=T.RNG_REFERENCE, flags=flags))
+        close = np.isclose(mean, osum / spp, rtol=1e-3, atol=1e-5).all(-1)
+        assert close.mean() > 0.97, (flags, close.mean())
+    # frames compose: [0,6) = [0,2) + [2,6)
+    a = T.render_scene(T.render_cfg(W, H, 2, 5, rng_mode=T.RNG_REFERENCE))
+    b = T.render_scene(T.render_cfg(W, H, 4, 5, rng_mode=T.RNG_REFERENCE, sample_offset=2))
+    assert np.allclose((2 * a + 4 * b) / 6, mean, atol=2e-6)
+
+
+@pytest.mark.parametrize("name,depth,nee", [("scene01", 5, False), ("scene01_lambert", 8, False),
+                                            ("scene01", 5, True), ("scene01_lambert", 8, True), ("scene02", 5, True)])
+def test_converged_image_gate(gpu, oracle, scenes, name, depth, nee):
+    """Independent streams (oracle: the reference's TEA+LCG; GPU: Philox), matched spp: mean relative
+    error < 1 %, no pixel beyond 4 sigma (one-in-16k outliers allowed for 3*W*H tests at 4 sigma)."""
+    T, s = gpu, scenes[name]
+    _load(T, s)
+    eye = SCENE_CAMERA[name]
+    W, H, spp = 128, 128, 256
+    osum, osq, _, _ = oracle.scene(s).render(oracle.cfg(W, H, spp, depth, eye=eye, at=(0, 5, eye[2] - 1)))
+    cfg = T.render_cfg(W, H, spp, depth, seed=9, eye=eye, at=(0, 5, eye[2] - 1), flags=T.FLAG_NEE if nee else 0)
+    mean, m2 = T.render_scene(cfg, moments=True)
+    rel, z = _gate(mean, m2, osum, osq, spp)
+    assert rel < 0.01, rel
+    assert (z > 4).mean() < 3e-4, ((z > 4).mean(), z.max())
+    assert z.max() < 6.5, z.max()
+
+
+def test_render_sample_ranges_and_device_accumulation(gpu, scenes):
+    """spp-split building block: disjoint Philox sample ranges accumulated into one device buffer
+    equal the single-call render (fp32 reassociation only)."""
+    import torch
+    T, s = gpu, scenes["scene01_lambert"]
+    _load(T, s)
+    W, H = 80, 48
+    full = T.render_scene(T.render_cfg(W, H, 12, 8, seed=3))
+    acc = torch.zeros(H, W, 4, device="cuda", dtype=torch.float32)
+    stream = torch.cuda.current_stream().cuda_stream
+    for off, n in ((0, 5), (5, 4), (9, 3)):
+        T.render_accumulate_device(T.render_cfg(W, H, n, 8, seed=3, sample_offset=off), acc.data_ptr(), 0, stream)
+    torch.cuda.synchronize()
+    a = acc.cpu().numpy()
+    assert (a[..., 3] == 12).all()
+    assert np.allclose(a[..., :3] / 12, full, atol=1e-6)
+    # other seed -> other image; same seed -> bit-identical image (deterministic reduce order)
+    assert not np.allclose(T.render_scene(T.render_cfg(W, H, 12, 8, seed=4)), full)
+    assert np.array_equal(T.render_scene(T.render_cfg(W, H, 12, 8, seed=3)), full)
+
+
+def test_render_ragged_sizes(gpu, oracle, scenes):
+    """Sizes that are not multiples of the 16x16 block tile or of 32 (the reference drops such edge
+    pixels, GraphicsRTX.cpp:209), 1x1, and a single sample."""
+    T, s = gpu, scenes["scene01"]
+    _load(T, s)
+    for (W, H, spp) in ((33, 17, 3), (1, 1, 4), (250, 3, 1)):
+        osum, _, _, _ = oracle.scene(s).render(oracle.cfg(W, H, spp, 5, rng_mode=1, seed=1))
+        mean = T.render_scene(T.render_cfg(W, H, spp, 5, seed=1))
+        close = np.isclose(mean, osum / spp, rtol=1e-3, atol=1e-5).all(-1)
+        assert close.mean() >= min(0.95, 1 - 1.5 / (W * H)), (W, H, close.mean())
+
+
+def test_sah_build_mode_gives_same_hits(gpu, oracle, scenes):
+    T, s = gpu, scenes["scene01"]
+    _load(T, s, T.BUILD_SAH)
+    rays = _random_rays(s, 1 << 16, seed=3)
+    tri, t, _, _, _ = oracle.scene(s).intersect(rays)
+    for variant in (T.ISECT_REFERENCE, T.ISECT_KD):
+        gtri, gt, _, _ = T.intersect_batch(rays, variant)
+        assert (gtri != tri).mean() < 1e-5

@@ -1,0 +1,111 @@
+"""CPU tests of the product's host side: the C-ABI library loads and exports every declared symbol,
+the KD builder reproduces the oracle's (= the reference's) tree, and GPU entry points fail loudly
+without a device.  No compute call is made here."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, heightfield
+
+
+def test_abi_exports_every_declared_symbol(tracer):
+    hdr = open(os.path.join(ROOT, "include", "mcpt.h")).read()
+    names = set(re.findall(r"\b(mcpt_[a-z_0-9]+)\s*\(", hdr))
+    assert len(names) >= 18
+    L = tracer.lib()
+    for n in sorted(names):
+        assert hasattr(L, n), f"libmcpt.so does not export {n}"
+    assert "sm_100a" in tracer.version()
+
+
+def test_struct_layouts_match_header(tracer):
+    # sizes the C compiler gives the structs of include/mcpt.h (checked with a tiny C program)
+    import subprocess, tempfile
+    src = '#include <stdio.h>\n#include "mcpt.h"\nint main(){printf("%zu %zu %zu %zu",sizeof(mcpt_scene_desc),sizeof(mcpt_render_cfg),sizeof(mcpt_counters),sizeof(mcpt_tree_info));return 0;}'
+    with tempfile.TemporaryDirectory() as d:
+        open(os.path.join(d, "s.c"), "w").write(src)
+        subprocess.check_call(["/usr/bin/gcc", "-I" + os.path.join(ROOT, "include"), os.path.join(d, "s.c"), "-o", os.path.join(d, "s")])
+        sizes = list(map(int, subprocess.check_output([os.path.join(d, "s")]).split()))
+    assert sizes == [C.sizeof(tracer.SceneDesc), C.sizeof(tracer.RenderCfg), C.sizeof(tracer.Counters), C.sizeof(tracer.TreeInfo)]
+
+
+@pytest.mark.parametrize("name", ["scene01", "scene01_lambert", "scene02", "scene03"])
+def test_host_builder_reproduces_reference_tree(tracer, oracle, scenes, name):
+    s = scenes[name]
+    tracer.create_geometry(s.verts, s.normals, s.tris, s.mats, tracer.BUILD_REFERENCE)
+    t, o = tracer.get_tree(), oracle.scene(s).tree()
+    assert np.array_equal(t.left, o.left) and np.array_equal(t.right, o.right)
+    assert np.array_equal(t.aabb.view(np.uint32), o.aabb.view(np.uint32))
+    assert np.array_equal(t.split_axis, o.split_axis)
+    assert np.array_equal(t.split_value.view(np.uint32), o.split_value.view(np.uint32))
+    assert np.array_equal(t.leaf_offset, o.leaf_offset) and np.array_equal(t.leaf_count, o.leaf_count)
+    assert np.array_equal(t.leaf_ids, o.leaf_ids)
+    info = tracer.tree_info()
+    assert info.num_nodes == len(o.left) and info.max_depth == o.max_depth
+    v, n, tr, m = tracer.get_scene()
+    assert np.array_equal(tr, s.tris) and np.array_equal(v, s.verts)
+    tracer.destroy_geometry()
+
+
+def test_host_builder_on_tessellated_surface(tracer, oracle):
+    from oracle.pyoracle import SceneArrays
+    verts, tri_v = heightfield(48)
+    tris = np.zeros((len(tri_v), 7), np.uint32)
+    tris[:, :3] = tri_v
+    s = SceneArrays(verts, np.array([[0, 1, 0]], np.float32), tris, np.zeros((1, 12), np.float32))
+    tracer.create_geometry(s.verts, s.normals, s.tris, s.mats)
+    t, o = tracer.get_tree(), oracle.scene(s).tree()
+    assert np.array_equal(t.left, o.left) and np.array_equal(t.leaf_ids, o.leaf_ids)
+    assert np.array_equal(t.aabb.view(np.uint32), o.aabb.view(np.uint32))
+    tracer.destroy_geometry()
+
+
+def test_scene_file_round_trip(tracer, scenes, tmp_path):
+    p = str(tmp_path / "s.mcpt")
+    scenes["scene02"].save(p)
+    tracer.load_scene_file(p)
+    v, n, t, m = tracer.get_scene()
+    assert np.array_equal(t, scenes["scene02"].tris) and np.array_equal(m, scenes["scene02"].mats)
+    assert tracer.tree_info().num_emitter_triangles == 4 * 420   # the four spherical lights
+    tracer.destroy_geometry()
+
+
+def test_errors_are_reported_not_thrown_across_the_abi(tracer, scenes, tmp_path):
+    s = scenes["scene01"]
+    with pytest.raises(tracer.McptError) as e:
+        tracer.create_geometry(s.verts, s.normals, np.zeros((0, 7), np.uint32), s.mats)
+    assert e.value.code == 1
+    bad = s.tris.copy()
+    bad[5, 1] = 10 ** 6
+    with pytest.raises(tracer.McptError, match="vertex index out of range"):
+        tracer.create_geometry(s.verts, s.normals, bad, s.mats)
+    with pytest.raises(tracer.McptError) as e:
+        tracer.load_scene_file(str(tmp_path / "missing.mcpt"))
+    assert e.value.code == 2
+    (tmp_path / "junk.mcpt").write_bytes(b"not a scene")
+    with pytest.raises(tracer.McptError):
+        tracer.load_scene_file(str(tmp_path / "junk.mcpt"))
+    with pytest.raises(tracer.McptError, match="no geometry"):
+        tracer.get_tree()
+
+
+def test_no_cpu_fallback(tracer, scenes):
+    """Without a CUDA device every compute entry point must refuse: the product has no CPU path."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is visible here")
+    s = scenes["scene01"]
+    tracer.create_geometry(s.verts, s.normals, s.tris, s.mats)
+    with pytest.raises(tracer.McptError) as e:
+        tracer.initialize(0)
+    assert e.value.code == tracer.ERR_NO_DEVICE
+    cfg = tracer.render_cfg(16, 16, 1, 5)
+    for call in (lambda: tracer.render_scene(cfg), lambda: tracer.intersect_batch(np.zeros((4, 6), np.float32)),
+                 lambda: tracer.primary_rays(cfg)):
+        with pytest.raises(tracer.McptError) as e:
+            call()
+        assert e.value.code == tracer.ERR_NO_DEVICE
+    tracer.destroy_geometry()

@@ -1,0 +1,155 @@
+"""CPU tests that pin the oracle (no GPU): known-answer vectors and the reference's own host code."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from conftest import heightfield
+
+# SURVEY.md 8(a5) / BASELINE.md section 2: statistics of the reference's own builder, measured with
+# the reference's KDTree.hpp compiled unmodified.
+TREE_STATS = {"scene01": (862, 4395, 2198, 4079, 20), "scene02": (1732, 7947, 3974, 7526, 32),
+              "scene03": (3024, 39201, 19601, 40055, 32)}
+
+
+def test_philox_known_answers(oracle):
+    # Random123 kat_vectors, philox4x32-10
+    kat = [([0, 0, 0, 0], [0, 0], [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]),
+           ([0xffffffff] * 4, [0xffffffff] * 2, [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]),
+           ([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0],
+            [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1])]
+    for ctr, key, want in kat:
+        assert oracle.philox(ctr, key).tolist() == want
+
+
+def test_park_miller_known_answer(oracle):
+    # rtx.hlsl:74-82 is the minimal-standard generator; Park & Miller's check value:
+    # starting from 1, the 10000th state is 1043618065.
+    sd = C.c_uint32(1)
+    for _ in range(10000):
+        oracle.L.oracle_rand_gen(C.byref(sd))
+    assert sd.value == 1043618065
+    sd = C.c_uint32(1)
+    assert oracle.L.oracle_rand_gen(C.byref(sd)) == np.float32(16807) / np.float32(2147483648.0)
+
+
+def test_tea_seed_avalanche(oracle):
+    # rtx.hlsl:61-72: neighbouring pixels / frames must decorrelate
+    a = np.array([oracle.L.oracle_rand_seed(i, 12345) for i in range(4096)], dtype=np.uint32)
+    assert len(np.unique(a)) == 4096
+    bits = np.unpackbits(a.view(np.uint8)).mean()
+    assert 0.48 < bits < 0.52
+
+
+def test_frame_seeds_are_mt19937_1234(oracle):
+    # GraphicsRTX.cpp:170-171,192
+    bg = np.random.MT19937()
+    bg._legacy_seeding(1234)
+    want = bg.random_raw(32).astype(np.uint32)
+    assert np.array_equal(oracle.frame_seeds(0, 32), want)
+    assert np.array_equal(oracle.frame_seeds(7, 5), want[7:12])
+
+
+@pytest.mark.parametrize("name", ["scene01", "scene02", "scene03"])
+def test_restated_builder_matches_survey_statistics(oracle, scenes, name):
+    t = oracle.scene(scenes[name]).tree()
+    ntri, nodes, leaves, refs, depth = TREE_STATS[name]
+    assert len(scenes[name].tris) == ntri
+    assert (len(t.left), t.num_leaves, len(t.leaf_ids), t.max_depth) == (nodes, leaves, refs, depth)
+
+
+@pytest.mark.parametrize("name,path", [
+    ("scene01", "/root/reference/MCRT/QuinEngine/Res/scene01.obj"),
+    ("scene02", "/root/reference/CVMCTracer/CVMCTracer/Resources/scene02.obj"),
+    ("scene03", "/root/reference/CVMCTracer/CVMCTracer/Resources/scene03.obj")])
+def test_restated_builder_equals_reference_builder(oracle, reference, scenes, name, path):
+    """Node for node (topology, boxes, planes, leaf id lists) against KDTree.hpp compiled from the reference."""
+    if not os.path.exists(path):
+        pytest.skip("reference not mounted")
+    h, s, _ = reference.load_obj(path)
+    # the committed fixture is what the reference's tinyobj produces
+    for a, b in ((s.verts, scenes[name].verts), (s.normals, scenes[name].normals), (s.tris, scenes[name].tris),
+                 (s.mats, scenes[name].mats)):
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    tr, _ = reference.build_tree(h)
+    assert tr.same_as(oracle.scene(s).tree())
+    reference.free(h)
+
+
+def test_restated_builder_equals_reference_on_heightfield(oracle, reference):
+    from oracle.pyoracle import SceneArrays
+    verts, tri_v = heightfield(40)
+    h = reference.from_arrays(verts, tri_v)
+    tr, _ = reference.build_tree(h)
+    tris = np.zeros((len(tri_v), 7), np.uint32)
+    tris[:, :3] = tri_v
+    s = SceneArrays(verts, np.array([[0, 1, 0]], np.float32), tris, np.zeros((1, 12), np.float32))
+    assert tr.same_as(oracle.scene(s).tree())
+    reference.free(h)
+
+
+def test_samplers_are_unit_and_in_lobe(oracle):
+    rng = np.random.default_rng(0)
+    out = np.zeros(3, np.float32)
+    for _ in range(200):
+        n = rng.normal(size=3)
+        n = (n / np.linalg.norm(n)).astype(np.float32)
+        u1, u2 = rng.uniform(0.01, 0.99, 2)
+        oracle.L.oracle_sample_hemi(u1, u2, n.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+        assert abs(np.linalg.norm(out) - 1) < 1e-4 and out @ n > -1e-5
+        # cos(theta) = sqrt(1 - u1)  (rtx.hlsl:283)
+        assert abs(out @ n - np.sqrt(1 - np.float32(u1))) < 2e-4
+    # the two special cases of the rotation (rtx.hlsl:287-292)
+    for n in ([0, 1, 0], [0, -1, 0]):
+        n = np.array(n, np.float32)
+        oracle.L.oracle_sample_hemi(0.3, 0.6, n.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+        assert out @ n > 0
+
+
+def test_fresnel_reflects_or_refracts(oracle):
+    n = np.array([0, 1, 0], np.float32)
+    d = np.array([0.6, -0.8, 0], np.float32)
+    out = np.zeros(3, np.float32)
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    # u above Tr' -> mirror reflection (rtx.hlsl:246-249)
+    oracle.L.oracle_sample_fresnel(0.999, p(n), p(d), 0.9, 1.5, p(out))
+    assert np.allclose(out, [0.6, 0.8, 0], atol=1e-6)
+    # u below Tr' -> Snell refraction entering (rtx.hlsl:223-227): sin_t = sin_i / Ni
+    oracle.L.oracle_sample_fresnel(0.001, p(n), p(d), 0.9, 1.5, p(out))
+    assert abs(out[0] - 0.6 / 1.5) < 1e-5 and out[1] < 0
+    assert abs(np.linalg.norm(out) - 1) < 1e-5
+
+
+def test_intersect_pixel_centre_rays_hit_expected_shapes(oracle, scenes):
+    """tinyobj shape order of scene01: ids 0-5 pWall1, 6-7 pWall2, 8-9 pWall3,
+    10-429 mirror sphere, 430-441 light, 442-861 glass sphere."""
+    sc = oracle.scene(scenes["scene01"])
+    cfg = oracle.cfg(64, 64, 1, 5, jitter=0)
+    rays = oracle.primary_rays(cfg)
+    assert np.allclose(rays[:, 2], 16.0)  # origin on the z = 16 plane
+    tri, t, b, g, cnt = sc.intersect(rays)
+    tri = tri.reshape(64, 64)
+    assert set(np.unique(tri[32, 2:6])) <= {8, 9}                                # red wall pWall3
+    assert set(np.unique(tri[32, -6:-2])) <= {6, 7}                              # blue wall pWall2
+    assert ((tri >= 430) & (tri <= 441)).any()                                   # the light is visible
+    assert ((tri >= 10) & (tri <= 429)).any() and (tri >= 442).any()             # both spheres
+    hit = tri >= 0
+    assert (t.reshape(64, 64)[hit] > 0).all() and cnt.rays == 64 * 64
+
+
+def test_render_is_deterministic_and_energy_bounded(oracle, scenes):
+    sc = oracle.scene(scenes["scene01"])
+    cfg = oracle.cfg(32, 32, 4, 5, threads=2)
+    s1, q1, d1, c1 = sc.render(cfg, display=True)
+    cfg.threads = 1
+    s2, q2, d2, c2 = sc.render(cfg, display=True)
+    assert np.array_equal(s1, s2) and np.array_equal(d1, d2) and c1.rays == c2.rays
+    assert s1.max() / 4 <= 0.8 + 1e-6      # no path can carry more than Ka = 0.8 (throughput <= 1 before RR)
+    assert c1.paths == 32 * 32 * 4 and c1.rays >= c1.paths
+    # the display value replays rtx.hlsl:401-402: after 4 frames it is (mean)^(1/2.2)
+    assert np.allclose(d1[..., :3], (s1 / 4) ** (1 / 2.2), atol=2e-3)
+    # sample ranges compose: frames [0,4) == [0,2) + [2,4)
+    a = oracle.cfg(32, 32, 2, 5)
+    b = oracle.cfg(32, 32, 2, 5, sample_offset=2)
+    assert np.allclose(sc.render(a)[0] + sc.render(b)[0], s1, rtol=0, atol=1e-12)
