@@ -57,7 +57,8 @@ enum {
     MCPT_FLAG_NEE = 1u,        /* next-event estimation to the emitters at Lambert vertices   */
     MCPT_FLAG_MOMENTS = 2u,    /* also accumulate per-pixel sum of squares                    */
     MCPT_FLAG_NO_JITTER = 4u,  /* pixel-corner rays ("bias = 0"), for the intersection gate   */
-    MCPT_FLAG_REF_TRAVERSAL = 8u /* render with the reference-order AABB traversal instead of the KD traversal */
+    MCPT_FLAG_REF_TRAVERSAL = 8u, /* render with the reference-order AABB traversal instead of the KD traversal */
+    MCPT_FLAG_SIMPLE_KERNEL = 16u /* one-ray-per-iteration kernel instead of the warp-voted state machine (A/B) */
 };
 
 /* Intersection kernels selectable through mcpt_intersect_batch. */
@@ -152,6 +153,9 @@ int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, vo
 int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays);
 
 int mcpt_get_counters(mcpt_counters* out);
+/* Measured FP32 FMA issue rate of the bound device in GFLOP/s (roofline denominator for the
+ * intersection / shading arithmetic; the reference publishes nothing comparable). */
+int mcpt_measure_fp32_peak(double* gflops);
 const char* mcpt_last_error(void);
 const char* mcpt_version(void);
 

@@ -2,6 +2,7 @@
 // Replaces PW::Tracer::RenderScene (CUTracer.cu:340-404) and the per-frame part of
 // GraphicsRTX::DoOnUpdate (GraphicsRTX.cpp:173-209): camera, frame seeds, launch, read-back.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 
@@ -20,6 +21,11 @@ int pick_chunks(int width, int height, int spp) {
     long long chunks = (target + pixels - 1) / pixels;
     chunks = std::max(1LL, std::min<long long>(chunks, spp));
     return static_cast<int>(std::min<long long>(chunks, 64));
+}
+
+int env_int(const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    return v && *v ? std::atoi(v) : dflt;
 }
 
 int check_cfg(const mcpt_render_cfg* cfg) {
@@ -67,6 +73,9 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.kd = (cfg->flags & MCPT_FLAG_REF_TRAVERSAL) == 0;
     r.nee = (cfg->flags & MCPT_FLAG_NEE) != 0;
     r.moments = moments;
+    r.state_machine = (cfg->flags & MCPT_FLAG_SIMPLE_KERNEL) == 0;
+    r.shade_threshold = env_int("MCPT_SM_SHADE", 12);
+    r.leaf_threshold = env_int("MCPT_SM_LEAF", 10);
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
         // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))
         // per frame, i.e. the raw generator output.
@@ -245,6 +254,28 @@ int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays) 
         return fail_cuda(e, "primary rays launch");
     if ((e = cudaMemcpyAsync(host_rays, c.d_rays.ptr, 6 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H rays");
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "primary rays");
+    return MCPT_OK;
+}
+
+int mcpt_measure_fp32_peak(double* gflops) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!gflops) return fail(MCPT_ERR_INVALID, "null gflops");
+    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    const int blocks = 148 * 16, iters = 1 << 14;
+    cudaError_t e;
+    if ((e = c.d_rgb.ensure(static_cast<size_t>(blocks) * 256)) != cudaSuccess) return fail_cuda(e, "alloc");
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        cudaEventRecord(c.ev[0], c.stream);
+        if ((e = launch_fp32_peak(c.d_rgb.ptr, blocks, iters, c.stream)) != cudaSuccess) return fail_cuda(e, "fp32 probe");
+        cudaEventRecord(c.ev[1], c.stream);
+        if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "fp32 probe");
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c.ev[0], c.ev[1]);
+        if (rep > 0) best = std::max(best, static_cast<double>(blocks) * 256 * iters * 16 / (ms * 1e6));
+    }
+    *gflops = best;
     return MCPT_OK;
 }
 

@@ -4,7 +4,7 @@
 #include "launch.h"
 
 #include "../../include/mcpt.h"
-#include "render.cuh"
+#include "render_sm.cuh"
 
 namespace mcpt {
 
@@ -62,6 +62,17 @@ __global__ void __launch_bounds__(256) finalize_kernel(const float4* __restrict_
     rgb[3 * i] = v.x * inv; rgb[3 * i + 1] = v.y * inv; rgb[3 * i + 2] = v.z * inv;
 }
 
+// FP32 issue-rate probe for the roofline denominator (MEASURED_PEAKS.json has no FP32
+// figure): 8 independent FMA chains per thread, 2 flops per FMA.
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* __restrict__ out, int iters, float x, float y) {
+    float a0 = threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    for (int i = 0; i < iters; ++i) {
+        a0 = __fmaf_rn(a0, x, y); a1 = __fmaf_rn(a1, x, y); a2 = __fmaf_rn(a2, x, y); a3 = __fmaf_rn(a3, x, y);
+        a4 = __fmaf_rn(a4, x, y); a5 = __fmaf_rn(a5, x, y); a6 = __fmaf_rn(a6, x, y); a7 = __fmaf_rn(a7, x, y);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+}
+
 template <class RNG, bool KD, bool NEE, bool MOMENTS>
 cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
@@ -74,8 +85,28 @@ cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+template <class RNG, bool NEE, bool MOMENTS>
+cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
+    RenderParams p;
+    p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
+    p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
+    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale;
+    p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
+    dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
+    render_kernel_sm<RNG, NEE, MOMENTS><<<grid, 256, 0, stream>>>(p, r.shade_threshold, r.leaf_threshold);
+    return cudaGetLastError();
+}
+
 template <class RNG>
 cudaError_t launch_render_rng(const RenderLaunch& r, cudaStream_t s) {
+    if (r.state_machine && r.kd) {
+        switch ((r.nee ? 2 : 0) | (r.moments ? 1 : 0)) {
+            case 0: return launch_render_sm_t<RNG, false, false>(r, s);
+            case 1: return launch_render_sm_t<RNG, false, true>(r, s);
+            case 2: return launch_render_sm_t<RNG, true, false>(r, s);
+            default: return launch_render_sm_t<RNG, true, true>(r, s);
+        }
+    }
     const int key = (r.kd ? 4 : 0) | (r.nee ? 2 : 0) | (r.moments ? 1 : 0);
     switch (key) {
         case 0: return launch_render_t<RNG, false, false, false>(r, s);
@@ -115,6 +146,11 @@ cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int
     if (n <= 0) return cudaSuccess;
     if (launches) ++*launches;
     intersect_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(sc, rays, n, variant, tri, t, beta, gamma);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fp32_peak(float* scratch, int blocks, int iters, cudaStream_t stream) {
+    fp32_peak_kernel<<<blocks, 256, 0, stream>>>(scratch, iters, 0.999f, 0.001f);
     return cudaGetLastError();
 }
 

@@ -21,6 +21,8 @@ struct RenderLaunch {
     unsigned long long* ray_counter;
     int rng_mode;          // MCPT_RNG_*
     bool kd, nee, moments;
+    bool state_machine;    // render_kernel_sm (warp-voted state machine) instead of render_kernel
+    int shade_threshold, leaf_threshold;
 };
 
 // Number of kernels launched is returned through *launches (adds to it).
@@ -38,5 +40,8 @@ cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int
 
 cudaError_t launch_primary_rays(const DCamera& cam, int width, int height, int sample, uint32_t seed, uint32_t jitter,
                                 int rng_mode, uint32_t frame_seed, float* rays, cudaStream_t stream, uint32_t* launches);
+
+// scratch: blocks*256 floats. flops = blocks*256*iters*16.
+cudaError_t launch_fp32_peak(float* scratch, int blocks, int iters, cudaStream_t stream);
 
 }  // namespace mcpt

@@ -1,0 +1,256 @@
+// Path-sampling kernel, warp-scheduled state-machine variant (the render path).
+//
+// ncu on the first kernel (render.cuh, one full ray per loop iteration, while-while traversal)
+// showed 4.9 of 32 lanes active per issued instruction: incoherent bounce rays need very different
+// numbers of node steps and leaf visits, and a warp waited for its slowest lane at every level
+// (profiles/r1a_*).  Here every lane is a small state machine
+//     INNER  at a KD node, needs one descent step            (cheap,  ~20 instructions)
+//     LEAF   inside a leaf, needs one triangle test            (medium, ~50)
+//     SHADE  ray finished, needs shading / the next ray        (heavy,  ~300)
+// and each loop iteration the WARP votes (ballot + popc) on ONE action to execute; lanes in other
+// states idle for that iteration only.  Cheap actions run eagerly, expensive ones wait until enough
+// lanes have queued up for them (thresholds below), so a lane that finishes its ray early is not
+// held back by the others' traversal, and a finished path regenerates the next camera sample in
+// place.  All path state lives in registers; only the traversal stack is in (L1-resident) local
+// memory.  Results are identical to render_kernel's: same rays, same arithmetic, same streams.
+#pragma once
+#include "render.cuh"
+
+namespace mcpt {
+
+#ifndef MCPT_SM_SHADE_THRESHOLD
+#define MCPT_SM_SHADE_THRESHOLD 12
+#endif
+#ifndef MCPT_SM_LEAF_THRESHOLD
+#define MCPT_SM_LEAF_THRESHOLD 10
+#endif
+
+enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
+
+template <class RNG, bool NEE, bool MOMENTS>
+__global__ void __launch_bounds__(256, 2) render_kernel_sm(const RenderParams p, const int shadeThreshold,
+                                                           const int leafThreshold) {
+    uint32_t px, py;
+    thread_pixel(px, py);
+    const bool inside = px < static_cast<uint32_t>(p.width) && py < static_cast<uint32_t>(p.height);
+    const uint32_t pixel = py * static_cast<uint32_t>(p.width) + px;
+    const int chunk = blockIdx.z;
+    const int base = p.sample_count / p.chunks, rem = p.sample_count % p.chunks;
+    const int local0 = chunk * base + min(chunk, rem);
+    const int localN = base + (chunk < rem ? 1 : 0);
+    int s = local0;
+    const int sEnd = local0 + localN;
+
+    // ---- per-lane state -------------------------------------------------------------------
+    RNG rng;
+    float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 1;  // the ray being traced
+    float ix = 0, iy = 0, iz = 1;                           // 1 / d
+    uint32_t nearBits = 0;                                  // bit a: d[a] < 0 -> the right child is nearer
+    float tmin = 0, tmax = 0, best = 10000.0f, hbeta = 0, hgamma = 0;
+    uint32_t htri = 0xFFFFFFFFu, node = 0, li = 0, lend = 0;
+    int top = 0;
+    uint2 stack[MCPT_KD_STACK];
+    F3 thr = f3(1, 1, 1), cur = f3(0, 0, 0), acc = f3(0, 0, 0), acc2 = f3(0, 0, 0);
+    F3 nextOrg = f3(0, 0, 0), nextDir = f3(0, 0, 1), shVal = f3(0, 0, 0);  // NEE: path ray parked behind the shadow ray
+    uint32_t shTri = 0, bounce = 0, nrays = 0;
+    bool shadow = false, lastWasNee = false;
+    uint32_t state = ST_DEAD;
+
+    // Prepares traversal of the ray (ox..dz): reciprocal, child order bits, clip against the root box.
+    auto begin_ray = [&]() {
+        ix = __fdiv_rn(1.0f, dx); iy = __fdiv_rn(1.0f, dy); iz = __fdiv_rn(1.0f, dz);
+        nearBits = (ix < 0.0f ? 1u : 0u) | (iy < 0.0f ? 2u : 0u) | (iz < 0.0f ? 4u : 0u);
+        tmin = 0.0f; tmax = 10000.0f;
+        float tn = (p.sc.bmin[0] - ox) * ix, tf = (p.sc.bmax[0] - ox) * ix;
+        if (ix < 0.0f) { const float sw = tn; tn = tf; tf = sw; }
+        tmin = fmaxf(tmin, tn); tmax = fminf(tmax, tf);  // fmaxf/fminf drop the NaN of 0 * inf
+        tn = (p.sc.bmin[1] - oy) * iy; tf = (p.sc.bmax[1] - oy) * iy;
+        if (iy < 0.0f) { const float sw = tn; tn = tf; tf = sw; }
+        tmin = fmaxf(tmin, tn); tmax = fminf(tmax, tf);
+        tn = (p.sc.bmin[2] - oz) * iz; tf = (p.sc.bmax[2] - oz) * iz;
+        if (iz < 0.0f) { const float sw = tn; tn = tf; tf = sw; }
+        tmin = fmaxf(tmin, tn); tmax = fminf(tmax, tf);
+        tmin *= (1.0f - 4e-7f); tmax *= (1.0f + 4e-7f);
+        best = 10000.0f; htri = 0xFFFFFFFFu; hbeta = 0; hgamma = 0;
+        node = 0; top = 0;
+        ++nrays;
+        state = (tmin <= tmax) ? ST_INNER : ST_SHADE;  // a ray that misses the scene box is shaded as a miss
+    };
+    auto start_sample = [&]() {
+        rng.start(pixel, p.seed, static_cast<uint32_t>(p.sample_begin + s), p.frame_seeds ? p.frame_seeds[s] : 0u);
+        float u1 = 0.5f, u2 = 0.5f;
+        if (p.jitter) { u1 = rng.next(); u2 = rng.next(); }
+        F3 o, d;
+        camera_ray(p.cam, p.width, p.height, px, py, u1, u2, o, d);
+        ox = o.x; oy = o.y; oz = o.z; dx = d.x; dy = d.y; dz = d.z;
+        thr = f3(1, 1, 1); cur = f3(0, 0, 0);
+        bounce = 0; lastWasNee = false; shadow = false;
+    };
+    // After a leaf: stop if the closest hit lies before the end of this cell, else continue with the
+    // next cell along the ray (cells are contiguous: its tmin is this cell's tmax).
+    auto pop_or_finish = [&]() {
+        if (best < tmax || top == 0) {
+            state = ST_SHADE;
+        } else {
+            --top;
+            node = stack[top].x;
+            tmin = tmax;
+            tmax = __uint_as_float(stack[top].y);
+            state = ST_INNER;
+        }
+    };
+
+    if (inside && s < sEnd) { start_sample(); begin_ray(); }
+
+    while (true) {
+        const uint32_t mI = __ballot_sync(0xFFFFFFFFu, state == ST_INNER);
+        const uint32_t mL = __ballot_sync(0xFFFFFFFFu, state == ST_LEAF);
+        const uint32_t mS = __ballot_sync(0xFFFFFFFFu, state == ST_SHADE);
+        if ((mI | mL | mS) == 0u) break;
+        const int nI = __popc(mI), nL = __popc(mL), nS = __popc(mS);
+
+        if (nS >= shadeThreshold || (nI | nL) == 0) {
+            // ================= SHADE: consume the hit, produce the next ray ====================
+            if (state == ST_SHADE) {
+                bool done = false, haveRay = false;
+                if (NEE && shadow) {
+                    if (htri == shTri) cur = cur + shVal;  // the sampled emitter point is visible
+                    shadow = false;
+                    ox = nextOrg.x; oy = nextOrg.y; oz = nextOrg.z; dx = nextDir.x; dy = nextDir.y; dz = nextDir.z;
+                    haveRay = true;
+                } else if (htri == 0xFFFFFFFFu) {
+                    done = true;  // rtx.hlsl:370
+                } else {
+                    rng.set_slot(bounce + 1u);
+                    if (bounce >= p.depth * 3u) {
+                        done = true;  // :313-316
+                    } else if (bounce >= p.depth) {
+                        const float illum = fmaxf(fmaxf(thr.x, thr.y), thr.z);  // :317-328
+                        if (illum > rng.next()) thr = thr / illum; else done = true;
+                    }
+                    if (!done) {
+                        const float4 s0 = ldg4(p.sc.tri_shade + 3 * htri);
+                        const uint32_t mat = __float_as_uint(s0.w);
+                        const float4 mKa = ldg4(p.sc.mats + 3 * mat);
+                        if (mKa.x > 0 || mKa.y > 0 || mKa.z > 0) {  // :329-334
+                            if (!(NEE && lastWasNee)) cur = cur + thr * f3(mKa.x, mKa.y, mKa.z) * p.emission_scale;
+                            done = true;
+                        } else {
+                            const float4 s1 = ldg4(p.sc.tri_shade + 3 * htri + 1), s2 = ldg4(p.sc.tri_shade + 3 * htri + 2);
+                            const float4 mKd = ldg4(p.sc.mats + 3 * mat + 1);
+                            F3 normal = f3(s0.x, s0.y, s0.z) * (1.0f - hbeta - hgamma) + f3(s1.x, s1.y, s1.z) * hbeta +
+                                        f3(s2.x, s2.y, s2.z) * hgamma;  // :336-340
+                            normal = normalize(normal);
+                            const F3 hp = f3(ox + best * dx, oy + best * dy, oz + best * dz);  // :197-199
+                            F3 dir = f3(dx, dy, dz);
+                            lastWasNee = false;
+                            if (mKd.w > 0) {  // Tr > 0, :342-346
+                                const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);
+                                dir = sample_fresnel(rng, normal, dir, mKd.w, mKs.w);
+                            } else if (mKa.w > 1) {  // Ns > 1, :348-352
+                                const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);
+                                dir = sample_phong(rng, normal, dir, mKa.w);
+                                thr = thr * f3(mKs.x, mKs.y, mKs.z);
+                            } else {  // :354-365
+                                const bool flip = dot(dir, normal) > 0;
+                                dir = flip ? -sample_hemi(rng, normal) : sample_hemi(rng, normal);
+                                thr = thr * f3(mKd.x, mKd.y, mKd.z);
+                                if (NEE && p.sc.num_emitters > 0 && bounce + 1u < p.depth * 3u) {
+                                    // what the reference would collect at bounce+1, gathered by area sampling
+                                    // of the emitters (DESIGN.md "next-event estimation")
+                                    rng.set_slot(0x80000000u | (bounce + 1u));
+                                    const float u0 = rng.next(), ub = rng.next(), uc = rng.next();
+                                    uint32_t e = 0;
+                                    while (e + 1 < p.sc.num_emitters && u0 > ldg4(p.sc.emitters + 3 * e + 1).w) ++e;
+                                    const float4 ea = ldg4(p.sc.emitters + 3 * e), eu = ldg4(p.sc.emitters + 3 * e + 1),
+                                                 ev = ldg4(p.sc.emitters + 3 * e + 2);
+                                    const float su = sqrtf(ub);
+                                    const float b1 = 1.0f - su, b2 = uc * su;
+                                    const F3 y = f3(ea.x + b1 * eu.x + b2 * ev.x, ea.y + b1 * eu.y + b2 * ev.y, ea.z + b1 * eu.z + b2 * ev.z);
+                                    F3 w = y - hp;
+                                    const float r2 = dot(w, w);
+                                    w = w * (1.0f / sqrtf(r2));
+                                    const F3 ng = f3(eu.y * ev.z - eu.z * ev.y, eu.z * ev.x - eu.x * ev.z, eu.x * ev.y - eu.y * ev.x);
+                                    const float cosy = fabsf(dot(ng, w)) / (2.0f * ea.w);
+                                    const float cosx = dot(flip ? -normal : normal, w);
+                                    if (cosx > 0 && cosy > 0 && r2 > 0) {
+                                        shTri = __float_as_uint(ev.w);
+                                        const uint32_t lmat = __float_as_uint(ldg4(p.sc.tri_shade + 3 * shTri).w);
+                                        const float4 lKa = ldg4(p.sc.mats + 3 * lmat);
+                                        const float g = cosx * cosy * p.sc.emitter_area / (MCPT_PI * r2);
+                                        shVal = thr * f3(lKa.x, lKa.y, lKa.z) * (g * p.emission_scale);
+                                        shadow = true;
+                                        nextOrg = hp + dir * 0.01f;  // the path ray waits behind the shadow ray
+                                        nextDir = dir;
+                                        const F3 so = hp + w * 0.01f;
+                                        ox = so.x; oy = so.y; oz = so.z; dx = w.x; dy = w.y; dz = w.z;
+                                    }
+                                    lastWasNee = true;
+                                }
+                            }
+                            if (!(NEE && shadow)) {
+                                const F3 no = hp + dir * 0.01f;  // :366
+                                ox = no.x; oy = no.y; oz = no.z; dx = dir.x; dy = dir.y; dz = dir.z;
+                            }
+                            ++bounce;
+                            haveRay = true;
+                        }
+                    }
+                }
+                if (done) {
+                    acc = acc + cur;
+                    if (MOMENTS) acc2 = acc2 + cur * cur;
+                    ++s;
+                    if (s < sEnd) { start_sample(); haveRay = true; } else state = ST_DEAD;
+                }
+                if (haveRay) begin_ray();
+            }
+        } else if (nL >= leafThreshold || nI == 0) {
+            // ================= LEAF: one triangle test ==========================================
+            if (state == ST_LEAF) {
+                const uint32_t id = __ldg(p.sc.leaf_ids + li);
+                float t, be, ga;
+                if (tri_test(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
+                    best = t; htri = id; hbeta = be; hgamma = ga;
+                }
+                if (++li == lend) pop_or_finish();
+            }
+        } else {
+            // ================= INNER: one node step =============================================
+            if (state == ST_INNER) {
+                const uint2 n = __ldg(p.sc.kd_nodes + node);
+                const uint32_t axis = n.y & 3u;
+                if (axis == 3u) {
+                    li = n.x; lend = n.x + (n.y >> 2);
+                    if (li == lend) pop_or_finish(); else state = ST_LEAF;
+                } else {
+                    const float oa = axis == 0u ? ox : (axis == 1u ? oy : oz);
+                    const float ia = axis == 0u ? ix : (axis == 1u ? iy : iz);
+                    const float tp = (__uint_as_float(n.x) - oa) * ia;
+                    const uint32_t nb = (nearBits >> axis) & 1u, left = n.y >> 2;
+                    const uint32_t nearChild = left + nb, farChild = left + (nb ^ 1u);
+                    if (tp > tmax) {
+                        node = nearChild;
+                    } else if (tp < tmin) {
+                        node = farChild;
+                    } else {
+                        stack[top] = make_uint2(farChild, __float_as_uint(tmax));
+                        ++top;
+                        tmax = tp;
+                        node = nearChild;
+                    }
+                }
+            }
+        }
+    }
+
+    if (inside) {
+        const size_t o = (static_cast<size_t>(chunk) * p.height + py) * p.width + px;
+        p.sum[o] = make_float4(acc.x, acc.y, acc.z, static_cast<float>(localN));
+        if (MOMENTS) p.sumsq[o] = make_float4(acc2.x, acc2.y, acc2.z, static_cast<float>(localN));
+    }
+    for (int off = 16; off > 0; off >>= 1) nrays += __shfl_xor_sync(0xFFFFFFFFu, nrays, off);
+    if ((threadIdx.x & 31u) == 0u && nrays) atomicAdd(p.ray_counter, static_cast<unsigned long long>(nrays));
+}
+
+}  // namespace mcpt

@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(HERE, "lib", "libmcpt.so")
 BUILD_REFERENCE, BUILD_SAH = 0, 1
 LOADER_TINYOBJ, LOADER_OBJREADER = 0, 1
 RNG_PHILOX, RNG_REFERENCE = 0, 1
-FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL = 1, 2, 4, 8
+FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL, FLAG_SIMPLE_KERNEL = 1, 2, 4, 8, 16
 ISECT_REFERENCE, ISECT_KD = 0, 1
 ERR_NO_DEVICE = 4
 
@@ -85,6 +85,7 @@ def lib() -> C.CDLL:
     L.mcpt_intersect_batch_device.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp]
     L.mcpt_primary_rays.argtypes = [C.POINTER(RenderCfg), C.c_int, _vp]
     L.mcpt_get_counters.argtypes = [C.POINTER(Counters)]
+    L.mcpt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
     L.mcpt_last_error.restype = C.c_char_p
     L.mcpt_version.restype = C.c_char_p
     _lib = L
@@ -236,6 +237,13 @@ def counters() -> Counters:
     c = Counters()
     _check(lib().mcpt_get_counters(C.byref(c)))
     return c
+
+
+def measure_fp32_peak() -> float:
+    """Measured FP32 FMA rate of the bound device, GFLOP/s."""
+    g = C.c_double()
+    _check(lib().mcpt_measure_fp32_peak(C.byref(g)))
+    return g.value
 
 
 def version() -> str:
