@@ -152,6 +152,9 @@ int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, vo
 /* Primary rays of one sample index exactly as the render kernel generates them (6 floats/pixel). */
 int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays);
 
+/* Work counters of one traversal variant over a host ray batch: out = {nodes popped, leaves (KD) or
+ * boxes (reference order) entered, triangle tests}.  Feeds the roofline's algorithmic-work figures. */
+int mcpt_traversal_stats(const float* rays, int64_t n, int variant, uint64_t out[3]);
 int mcpt_get_counters(mcpt_counters* out);
 /* Measured FP32 FMA issue rate of the bound device in GFLOP/s (roofline denominator for the
  * intersection / shading arithmetic; the reference publishes nothing comparable). */

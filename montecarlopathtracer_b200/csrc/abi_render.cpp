@@ -54,7 +54,7 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     cudaError_t e;
     if ((e = c.d_slices.ensure(pixels * chunks)) != cudaSuccess) return fail_cuda(e, "alloc slices");
     if (moments && (e = c.d_slices_sq.ensure(pixels * chunks)) != cudaSuccess) return fail_cuda(e, "alloc slices_sq");
-    if ((e = c.d_counter.ensure(1)) != cudaSuccess) return fail_cuda(e, "alloc counter");
+    if ((e = c.d_counter.ensure(4)) != cudaSuccess) return fail_cuda(e, "alloc counter");
     if ((e = cudaMemsetAsync(c.d_counter.ptr, 0, sizeof(unsigned long long), stream)) != cudaSuccess) return fail_cuda(e, "memset");
 
     RenderLaunch r;
@@ -254,6 +254,25 @@ int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays) 
         return fail_cuda(e, "primary rays launch");
     if ((e = cudaMemcpyAsync(host_rays, c.d_rays.ptr, 6 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H rays");
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "primary rays");
+    return MCPT_OK;
+}
+
+int mcpt_traversal_stats(const float* rays, int64_t n, int variant, uint64_t out[3]) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (n <= 0 || !rays || !out) return fail(MCPT_ERR_INVALID, "bad ray batch");
+    int rc = ensure_uploaded();
+    if (rc) return rc;
+    const size_t N = static_cast<size_t>(n);
+    cudaError_t e;
+    if ((e = c.d_rays.ensure(6 * N)) != cudaSuccess || (e = c.d_counter.ensure(4)) != cudaSuccess) return fail_cuda(e, "alloc");
+    if ((e = cudaMemcpyAsync(c.d_rays.ptr, rays, 6 * N * sizeof(float), cudaMemcpyHostToDevice, c.stream)) != cudaSuccess) return fail_cuda(e, "H2D rays");
+    if ((e = cudaMemsetAsync(c.d_counter.ptr, 0, 4 * sizeof(unsigned long long), c.stream)) != cudaSuccess) return fail_cuda(e, "memset");
+    if ((e = launch_tally(c.dscene, c.d_rays.ptr, n, variant, c.d_counter.ptr, c.stream)) != cudaSuccess) return fail_cuda(e, "tally launch");
+    unsigned long long h[3];
+    if ((e = cudaMemcpyAsync(h, c.d_counter.ptr, sizeof(h), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H");
+    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "tally");
+    out[0] = h[0]; out[1] = h[1]; out[2] = h[2];
     return MCPT_OK;
 }
 

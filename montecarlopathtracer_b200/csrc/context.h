@@ -50,7 +50,7 @@ struct Context {
     DeviceBuffer<float4> d_slices, d_slices_sq, d_sum, d_sumsq;
     DeviceBuffer<float> d_rgb;
     DeviceBuffer<uint32_t> d_frame_seeds;
-    DeviceBuffer<unsigned long long> d_counter;
+    DeviceBuffer<unsigned long long> d_counter;  // >= 4 entries
     // intersect scratch
     DeviceBuffer<float> d_rays, d_t, d_beta, d_gamma;
     DeviceBuffer<int32_t> d_tri;

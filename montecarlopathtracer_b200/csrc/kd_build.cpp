@@ -144,10 +144,12 @@ void decide(const HostScene& scene, const std::vector<Box>& triBox, const BuildN
 
 }  // namespace
 
+void build_sah_tree(const HostScene& scene, HostTree& out);  // kd_build_sah.cpp
+
 void build_kd_tree(const HostScene& scene, int mode, HostTree& out) {
+    if (mode == 1) { build_sah_tree(scene, out); return; }
     auto t0 = std::chrono::steady_clock::now();
     Params params;
-    if (mode == 1) params.traversal_cost = 0.25f;  // own tree: stop splitting when it barely pays
     const size_t nT = scene.num_triangles();
     std::vector<Box> triBox(nT);
 #pragma omp parallel for schedule(static) if (nT >= 65536)

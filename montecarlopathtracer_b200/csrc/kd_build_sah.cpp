@@ -1,0 +1,283 @@
+// MCPT_BUILD_SAH: this library's own KD-tree builder (product code, no reference counterpart).
+//
+// The reference tree (kd_build.cpp, KDTree.hpp:58-287) bins a triangle by its WHOLE bounding box:
+// a sphere triangle is referenced by every cell its box overlaps, median planes are used above 64
+// triangles and Cts = 0 keeps splitting until duplication explodes.  It stays the parity
+// anchor.  For rendering, the same hits can be found with far fewer node steps and triangle tests:
+//   * surface-area heuristic on every level, sweep over sorted bound events (Wald & Havran 2006);
+//   * "perfect splits": a straddling triangle is CLIPPED to each child cell (Sutherland-Hodgman in
+//     double, bounds rounded outwards), so it is referenced only where it really is;
+//   * empty-space bonus, traversal/intersection cost ratio tuned for the strict Cramer test;
+//   * depth cap 31 so the traversal stack (MCPT_KD_STACK = 32) can never overflow.
+// Output uses the same flattened layout as the reference tree (BFS order, children adjacent, ids
+// ascending inside a leaf); the per-node box is the cell.
+#include <omp.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cfloat>
+
+#include "host_scene.h"
+
+namespace mcpt {
+namespace {
+
+struct Box {
+    float lo[3], hi[3];
+};
+
+struct Ref {
+    uint32_t id;
+    Box b;  // bounds of the triangle clipped to the current cell
+};
+
+struct Node {
+    Box cell;
+    int axis = -1;
+    float plane = 0.0f;
+    int left = -1, right = -1;
+    std::vector<uint32_t> ids;
+};
+
+const float kTraversalCost = 1.0f;
+const float kIntersectCost = 2.5f;   // the strict Cramer test + its three dependent loads vs one plane step
+const float kEmptyBonus = 0.8f;
+
+inline float surface(const Box& b) {
+    const float x = b.hi[0] - b.lo[0], y = b.hi[1] - b.lo[1], z = b.hi[2] - b.lo[2];
+    return 2.0f * (x * y + y * z + z * x);
+}
+
+// Bounds of triangle `id` clipped to `cell` (conservative: rounded outwards, then clamped to the cell).
+bool clipped_bounds(const HostScene& s, uint32_t id, const Box& cell, Box& out) {
+    double poly[16][3], tmp[16][3];
+    int n = 3;
+    for (int k = 0; k < 3; ++k) {
+        const float* v = s.vertex(id, k);
+        for (int i = 0; i < 3; ++i) poly[k][i] = v[i];
+    }
+    for (int axis = 0; axis < 3 && n > 0; ++axis) {
+        for (int side = 0; side < 2 && n > 0; ++side) {
+            const double plane = side == 0 ? cell.lo[axis] : cell.hi[axis];
+            const double sign = side == 0 ? 1.0 : -1.0;  // keep sign * (x - plane) >= 0
+            int m = 0;
+            for (int k = 0; k < n; ++k) {
+                const double* a = poly[k];
+                const double* b = poly[(k + 1) % n];
+                const double da = sign * (a[axis] - plane), db = sign * (b[axis] - plane);
+                if (da >= 0) { for (int i = 0; i < 3; ++i) tmp[m][i] = a[i]; ++m; }
+                if ((da > 0 && db < 0) || (da < 0 && db > 0)) {
+                    const double t = da / (da - db);
+                    for (int i = 0; i < 3; ++i) tmp[m][i] = a[i] + t * (b[i] - a[i]);
+                    tmp[m][axis] = plane;
+                    ++m;
+                }
+            }
+            n = m;
+            for (int k = 0; k < n; ++k) for (int i = 0; i < 3; ++i) poly[k][i] = tmp[k][i];
+        }
+    }
+    if (n == 0) return false;
+    for (int i = 0; i < 3; ++i) {
+        double lo = poly[0][i], hi = poly[0][i];
+        for (int k = 1; k < n; ++k) { lo = std::min(lo, poly[k][i]); hi = std::max(hi, poly[k][i]); }
+        float flo = static_cast<float>(lo), fhi = static_cast<float>(hi);
+        if (flo > lo) flo = std::nextafter(flo, -FLT_MAX);
+        if (fhi < hi) fhi = std::nextafter(fhi, FLT_MAX);
+        out.lo[i] = std::max(flo, cell.lo[i]);
+        out.hi[i] = std::min(fhi, cell.hi[i]);
+        if (out.lo[i] > out.hi[i]) return false;
+    }
+    return true;
+}
+
+struct Event {
+    float pos;
+    int type;  // 0 = end, 1 = planar, 2 = start
+};
+
+struct Split {
+    float cost = FLT_MAX;
+    int axis = -1;
+    float plane = 0.0f;
+    bool planarLeft = true;
+};
+
+Split find_split(const Box& cell, const std::vector<Ref>& refs, std::vector<Event>& ev) {
+    Split best;
+    const float invSA = 1.0f / surface(cell);
+    const int n = static_cast<int>(refs.size());
+    for (int axis = 0; axis < 3; ++axis) {
+        if (!(cell.hi[axis] > cell.lo[axis])) continue;
+        ev.clear();
+        for (const Ref& r : refs) {
+            if (r.b.lo[axis] == r.b.hi[axis]) {
+                ev.push_back({r.b.lo[axis], 1});
+            } else {
+                ev.push_back({r.b.lo[axis], 2});
+                ev.push_back({r.b.hi[axis], 0});
+            }
+        }
+        std::sort(ev.begin(), ev.end(), [](const Event& a, const Event& b) { return a.pos < b.pos || (a.pos == b.pos && a.type < b.type); });
+        int nl = 0, nr = n;
+        for (size_t i = 0; i < ev.size();) {
+            const float pos = ev[i].pos;
+            int ends = 0, planar = 0, starts = 0;
+            while (i < ev.size() && ev[i].pos == pos && ev[i].type == 0) { ++ends; ++i; }
+            while (i < ev.size() && ev[i].pos == pos && ev[i].type == 1) { ++planar; ++i; }
+            while (i < ev.size() && ev[i].pos == pos && ev[i].type == 2) { ++starts; ++i; }
+            nr -= planar + ends;
+            if (pos > cell.lo[axis] && pos < cell.hi[axis]) {
+                Box l = cell, r = cell;
+                l.hi[axis] = pos;
+                r.lo[axis] = pos;
+                const float pl = surface(l) * invSA, pr = surface(r) * invSA;
+                for (int side = 0; side < 2; ++side) {
+                    const int cl = nl + (side == 0 ? planar : 0), cr = nr + (side == 1 ? planar : 0);
+                    float c = kTraversalCost + kIntersectCost * (pl * cl + pr * cr);
+                    if (cl == 0 || cr == 0) c *= kEmptyBonus;
+                    if (c < best.cost) { best.cost = c; best.axis = axis; best.plane = pos; best.planarLeft = side == 0; }
+                    if (planar == 0) break;
+                }
+            }
+            nl += starts + planar;
+        }
+    }
+    return best;
+}
+
+void build_node(const HostScene& s, std::vector<Node>& nodes, int me, std::vector<Ref>& refs, int depth, int maxDepth) {
+    std::vector<Event> ev;
+    const size_t n = refs.size();
+    Split sp;
+    if (n > 0 && depth < maxDepth) sp = find_split(nodes[me].cell, refs, ev);
+    if (sp.axis < 0 || sp.cost >= kIntersectCost * static_cast<float>(n)) {
+        nodes[me].ids.reserve(n);
+        for (const Ref& r : refs) nodes[me].ids.push_back(r.id);
+        std::sort(nodes[me].ids.begin(), nodes[me].ids.end());
+        return;
+    }
+    const int a = sp.axis;
+    Box lc = nodes[me].cell, rc = nodes[me].cell;
+    lc.hi[a] = sp.plane;
+    rc.lo[a] = sp.plane;
+    std::vector<Ref> lrefs, rrefs;
+    for (const Ref& r : refs) {
+        if (r.b.lo[a] == r.b.hi[a] && r.b.lo[a] == sp.plane) {
+            (sp.planarLeft ? lrefs : rrefs).push_back(r);
+        } else if (r.b.hi[a] <= sp.plane) {
+            lrefs.push_back(r);
+        } else if (r.b.lo[a] >= sp.plane) {
+            rrefs.push_back(r);
+        } else {
+            Ref c{r.id, {}};
+            if (clipped_bounds(s, r.id, lc, c.b)) lrefs.push_back(c);
+            if (clipped_bounds(s, r.id, rc, c.b)) rrefs.push_back(c);
+        }
+    }
+    std::vector<Ref>().swap(refs);
+    int li = -1, ri = -1;
+#pragma omp critical(mcpt_sah_nodes)
+    if (nodes.size() + 2 <= nodes.capacity()) {  // never reallocate: other tasks read their own nodes concurrently
+        li = static_cast<int>(nodes.size());
+        ri = li + 1;
+        nodes.emplace_back();
+        nodes.emplace_back();
+        nodes[li].cell = lc;
+        nodes[ri].cell = rc;
+        nodes[me].axis = a;
+        nodes[me].plane = sp.plane;
+        nodes[me].left = li;
+        nodes[me].right = ri;
+    }
+    if (li < 0) {  // node budget exhausted (pathological duplication): stop here
+        for (const Ref& r : lrefs) nodes[me].ids.push_back(r.id);
+        for (const Ref& r : rrefs) nodes[me].ids.push_back(r.id);
+        std::sort(nodes[me].ids.begin(), nodes[me].ids.end());
+        nodes[me].ids.erase(std::unique(nodes[me].ids.begin(), nodes[me].ids.end()), nodes[me].ids.end());
+        return;
+    }
+    const bool spawn = lrefs.size() + rrefs.size() > 4096;
+#pragma omp task shared(s, nodes) firstprivate(li, depth, maxDepth) if (spawn)
+    {
+        std::vector<Ref> mine;
+        mine.swap(lrefs);
+        build_node(s, nodes, li, mine, depth + 1, maxDepth);
+    }
+    build_node(s, nodes, ri, rrefs, depth + 1, maxDepth);
+#pragma omp taskwait
+}
+
+}  // namespace
+
+void build_sah_tree(const HostScene& scene, HostTree& out) {
+    auto t0 = std::chrono::steady_clock::now();
+    const size_t nT = scene.num_triangles();
+    std::vector<Ref> refs(nT);
+    Box root = {{FLT_MAX, FLT_MAX, FLT_MAX}, {-FLT_MAX, -FLT_MAX, -FLT_MAX}};
+    for (size_t t = 0; t < nT; ++t) {
+        Box b = {{FLT_MAX, FLT_MAX, FLT_MAX}, {-FLT_MAX, -FLT_MAX, -FLT_MAX}};
+        for (int k = 0; k < 3; ++k) {
+            const float* v = scene.vertex(static_cast<uint32_t>(t), k);
+            for (int i = 0; i < 3; ++i) { b.lo[i] = std::min(b.lo[i], v[i]); b.hi[i] = std::max(b.hi[i], v[i]); }
+        }
+        refs[t] = {static_cast<uint32_t>(t), b};
+        for (int i = 0; i < 3; ++i) { root.lo[i] = std::min(root.lo[i], b.lo[i]); root.hi[i] = std::max(root.hi[i], b.hi[i]); }
+    }
+    const int maxDepth = std::min(31, static_cast<int>(8.0 + 1.3 * std::log2(static_cast<double>(std::max<size_t>(nT, 1)))));
+    // std::vector<Node> would move nodes while tasks hold indices only (never references across the
+    // critical section), so growth is safe; reserve to keep it cheap.
+    std::vector<Node> nodes;
+    nodes.reserve(6 * nT + 1024);
+    nodes.emplace_back();
+    nodes[0].cell = root;
+#pragma omp parallel
+#pragma omp single
+    build_node(scene, nodes, 0, refs, 0, maxDepth);
+
+    // breadth-first renumbering, children adjacent (same layout as the reference flatten)
+    std::vector<int> order;
+    order.reserve(nodes.size());
+    std::vector<uint32_t> depthOf;
+    order.push_back(0);
+    depthOf.push_back(0);
+    std::vector<int> newIndex(nodes.size(), -1);
+    for (size_t k = 0; k < order.size(); ++k) {
+        const Node& n = nodes[static_cast<size_t>(order[k])];
+        newIndex[static_cast<size_t>(order[k])] = static_cast<int>(k);
+        if (n.axis >= 0) {
+            order.push_back(n.left); depthOf.push_back(depthOf[k] + 1);
+            order.push_back(n.right); depthOf.push_back(depthOf[k] + 1);
+        }
+    }
+    out = HostTree();
+    const size_t nN = order.size();
+    out.left.resize(nN); out.aabb.resize(6 * nN); out.split_axis.resize(nN); out.split_value.resize(nN);
+    out.leaf_offset.resize(nN); out.leaf_count.resize(nN);
+    // children of node k are the next two unassigned BFS slots: recompute positions
+    size_t next = 1;
+    for (size_t k = 0; k < nN; ++k) {
+        const Node& n = nodes[static_cast<size_t>(order[k])];
+        for (int i = 0; i < 3; ++i) { out.aabb[6 * k + i] = n.cell.lo[i]; out.aabb[6 * k + 3 + i] = n.cell.hi[i]; }
+        out.leaf_offset[k] = static_cast<uint32_t>(out.leaf_ids.size());
+        out.max_depth = std::max(out.max_depth, depthOf[k]);
+        if (n.axis >= 0) {
+            out.left[k] = static_cast<uint32_t>(next);
+            next += 2;
+            out.split_axis[k] = static_cast<uint32_t>(n.axis + 1);
+            out.split_value[k] = n.plane;
+            out.leaf_count[k] = 0;
+        } else {
+            out.left[k] = 0xFFFFFFFFu;
+            out.split_axis[k] = 0;
+            out.split_value[k] = 0.0f;
+            out.leaf_count[k] = static_cast<uint32_t>(n.ids.size());
+            out.leaf_ids.insert(out.leaf_ids.end(), n.ids.begin(), n.ids.end());
+            ++out.num_leaves;
+        }
+    }
+    out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+}  // namespace mcpt

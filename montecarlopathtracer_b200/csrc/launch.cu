@@ -25,6 +25,24 @@ __global__ void __launch_bounds__(256) intersect_kernel(const DScene sc, const f
     if (gamma) gamma[i] = h.gamma;
 }
 
+// Work counters of one traversal variant over a ray batch: {nodes popped, leaves/boxes entered,
+// triangle tests} -- the per-ray figures the roofline's algorithmic work is stated in.
+__global__ void __launch_bounds__(256) tally_kernel(const DScene sc, const float* __restrict__ rays, int64_t n, int variant,
+                                                    unsigned long long* __restrict__ out) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    TraversalTally tally;
+    if (i < n) {
+        const float* r = rays + 6 * i;
+        if (variant == MCPT_ISECT_KD) intersect_kd(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
+        else intersect_ref(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
+    }
+    uint32_t a = tally.popped, b = tally.entered, c = tally.tris;
+    for (int off = 16; off > 0; off >>= 1) {
+        a += __shfl_xor_sync(0xFFFFFFFFu, a, off); b += __shfl_xor_sync(0xFFFFFFFFu, b, off); c += __shfl_xor_sync(0xFFFFFFFFu, c, off);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicAdd(out, (unsigned long long)a); atomicAdd(out + 1, (unsigned long long)b); atomicAdd(out + 2, (unsigned long long)c); }
+}
+
 template <class RNG>
 __global__ void __launch_bounds__(256) primary_rays_kernel(const DCamera cam, int width, int height, uint32_t sample,
                                                            uint32_t seed, uint32_t jitter, uint32_t frameSeed,
@@ -146,6 +164,12 @@ cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int
     if (n <= 0) return cudaSuccess;
     if (launches) ++*launches;
     intersect_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(sc, rays, n, variant, tri, t, beta, gamma);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tally(const DScene& sc, const float* rays, int64_t n, int variant, unsigned long long* out, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    tally_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(sc, rays, n, variant, out);
     return cudaGetLastError();
 }
 

@@ -41,6 +41,8 @@ cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int
 cudaError_t launch_primary_rays(const DCamera& cam, int width, int height, int sample, uint32_t seed, uint32_t jitter,
                                 int rng_mode, uint32_t frame_seed, float* rays, cudaStream_t stream, uint32_t* launches);
 
+cudaError_t launch_tally(const DScene& sc, const float* rays, int64_t n, int variant, unsigned long long* out3, cudaStream_t stream);
+
 // scratch: blocks*256 floats. flops = blocks*256*iters*16.
 cudaError_t launch_fp32_peak(float* scratch, int blocks, int iters, cudaStream_t stream);
 

@@ -85,6 +85,7 @@ def lib() -> C.CDLL:
     L.mcpt_intersect_batch_device.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp]
     L.mcpt_primary_rays.argtypes = [C.POINTER(RenderCfg), C.c_int, _vp]
     L.mcpt_get_counters.argtypes = [C.POINTER(Counters)]
+    L.mcpt_traversal_stats.argtypes = [_vp, C.c_int64, C.c_int, _vp]
     L.mcpt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
     L.mcpt_last_error.restype = C.c_char_p
     L.mcpt_version.restype = C.c_char_p
@@ -237,6 +238,14 @@ def counters() -> Counters:
     c = Counters()
     _check(lib().mcpt_get_counters(C.byref(c)))
     return c
+
+
+def traversal_stats(rays: np.ndarray, variant: int = ISECT_KD):
+    """-> (nodes popped, leaves/boxes entered, triangle tests) summed over the batch."""
+    rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+    out = np.zeros(3, np.uint64)
+    _check(lib().mcpt_traversal_stats(_p(rays), len(rays), variant, _p(out)))
+    return tuple(int(x) for x in out)
 
 
 def measure_fp32_peak() -> float:
