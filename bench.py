@@ -149,6 +149,7 @@ def main():
     ap.add_argument("--workload", default="K2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (a reduced-spp run is NOT the headline number)")
     ap.add_argument("--flags", default="", help="comma list: nee,ref_traversal")
+    ap.add_argument("--tree", default="sah", choices=["sah", "reference"], help="KD builder for the render path (same hits either way)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -176,7 +177,8 @@ def main():
         flags |= {"nee": T.FLAG_NEE, "ref_traversal": T.FLAG_REF_TRAVERSAL}[f]
 
     T.initialize(local)
-    T.load_scene_file(os.path.join(ROOT, "scenes", scene_file))
+    build_mode = T.BUILD_REFERENCE if args.tree == "reference" else T.BUILD_SAH
+    T.load_scene_file(os.path.join(ROOT, "scenes", scene_file), build_mode)
     info = T.tree_info()
     v, n, tr, m = T.get_scene()   # host tables for the e2e leg
 
@@ -232,11 +234,11 @@ def main():
     host = np.empty((H, W, 3), np.float32)
     e2e_cfg = T.render_cfg(W, H, spp, depth, seed=0, sample_offset=rank * spp, flags=flags, eye=(0, 5, eyez), at=(0, 5, eyez - 1))
     e2e_steps = max(1, min(args.steps, 2))
-    T.create_geometry(v, n, tr, m); T.render_scene(e2e_cfg, host)      # warm
+    T.create_geometry(v, n, tr, m, build_mode); T.render_scene(e2e_cfg, host)      # warm
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        T.create_geometry(v, n, tr, m)     # CreateGeometry: host tables -> tree -> H2D
+        T.create_geometry(v, n, tr, m, build_mode)     # CreateGeometry: host tables -> tree -> H2D
         T.render_scene(e2e_cfg, host)      # RenderScene: kernel -> D2H of the image
         launches_e2e = T.counters().launches
     torch.cuda.synchronize()
@@ -259,6 +261,7 @@ def main():
                        "spp_per_gpu": spp, "parallelism": f"spp-split x{world}, one NCCL reduce" if world > 1 else "1 GPU",
                        "estimator": "NEE" if flags & T.FLAG_NEE else "emission-on-hit (reference)", "rng": "philox4x32-10",
                        "l2": "flushed between timed steps (256 MiB memset); scene is L1/L2-resident by design",
+                       "tree": "own SAH builder (MCPT_BUILD_SAH)" if build_mode == T.BUILD_SAH else "reference-rule tree (MCPT_BUILD_REFERENCE)",
                        "tree_nodes": info.num_nodes, "scene_bytes_hbm": int(info.device_bytes)},
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(info.device_bytes),
                     "d2h_bytes_per_step": W * H * 3 * 4, "steps": e2e_steps},

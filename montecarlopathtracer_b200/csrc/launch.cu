@@ -111,7 +111,9 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
-    render_kernel_sm<RNG, NEE, MOMENTS><<<grid, 256, 0, stream>>>(p, r.shade_threshold, r.leaf_threshold);
+    if (r.min_blocks >= 4) render_kernel_sm<RNG, NEE, MOMENTS, 4><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
+    else if (r.min_blocks == 3) render_kernel_sm<RNG, NEE, MOMENTS, 3><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
+    else render_kernel_sm<RNG, NEE, MOMENTS, 2><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
     return cudaGetLastError();
 }
 

@@ -22,7 +22,8 @@ struct RenderLaunch {
     int rng_mode;          // MCPT_RNG_*
     bool kd, nee, moments;
     bool state_machine;    // render_kernel_sm (warp-voted state machine) instead of render_kernel
-    int shade_threshold, leaf_threshold;
+    int shade_threshold;   // lanes that must be waiting before the warp leaves the traverse phase
+    int min_blocks;        // 2, 3 or 4 resident 256-thread blocks per SM (register cap 128 / 85 / 64)
 };
 
 // Number of kernels launched is returned through *launches (adds to it).

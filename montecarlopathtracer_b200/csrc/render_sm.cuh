@@ -1,35 +1,27 @@
-// Path-sampling kernel, warp-scheduled state-machine variant (the render path).
+// Path-sampling kernel, persistent-lane variant (the render path).
 //
-// ncu on the first kernel (render.cuh, one full ray per loop iteration, while-while traversal)
-// showed 4.9 of 32 lanes active per issued instruction: incoherent bounce rays need very different
-// numbers of node steps and leaf visits, and a warp waited for its slowest lane at every level
-// (profiles/r1a_*).  Here every lane is a small state machine
-//     INNER  at a KD node, needs one descent step            (cheap,  ~20 instructions)
-//     LEAF   inside a leaf, needs one triangle test            (medium, ~50)
-//     SHADE  ray finished, needs shading / the next ray        (heavy,  ~300)
-// and each loop iteration the WARP votes (ballot + popc) on ONE action to execute; lanes in other
-// states idle for that iteration only.  Cheap actions run eagerly, expensive ones wait until enough
-// lanes have queued up for them (thresholds below), so a lane that finishes its ray early is not
-// held back by the others' traversal, and a finished path regenerates the next camera sample in
-// place.  All path state lives in registers; only the traversal stack is in (L1-resident) local
-// memory.  Results are identical to render_kernel's: same rays, same arithmetic, same streams.
+// ncu on the first kernel (render.cuh: one whole ray per loop iteration) showed 4.9 of 32 lanes
+// active per issued instruction (profiles/r1a_*): incoherent bounce rays need very different numbers
+// of node steps and leaf visits, and at every trace call the warp waited for its slowest lane.
+// Here a lane keeps its traversal state (node, interval, stack, closest hit) in registers ACROSS
+// loop iterations and the warp alternates two phases:
+//   TRAVERSE  every lane with a ray in flight advances it by one leaf visit (descend to the next
+//             leaf, test its triangles, pop); after each visit the warp votes (ballot + popc) and
+//             leaves the phase as soon as `shadeThreshold` lanes have finished their rays;
+//   SHADE     those lanes consume their hit (Russian roulette, emitter test, BSDF sample, optional
+//             shadow ray, or the next camera sample) and start a new ray; the others keep theirs.
+// A finished lane therefore waits for at most a few leaf visits of its neighbours instead of for
+// their whole traversal, and shading runs with at least `shadeThreshold` lanes.  Same rays, same
+// arithmetic, same random streams as render_kernel: the images are bit-identical.
 #pragma once
 #include "render.cuh"
 
 namespace mcpt {
 
-#ifndef MCPT_SM_SHADE_THRESHOLD
-#define MCPT_SM_SHADE_THRESHOLD 12
-#endif
-#ifndef MCPT_SM_LEAF_THRESHOLD
-#define MCPT_SM_LEAF_THRESHOLD 10
-#endif
-
 enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 
-template <class RNG, bool NEE, bool MOMENTS>
-__global__ void __launch_bounds__(256, 2) render_kernel_sm(const RenderParams p, const int shadeThreshold,
-                                                           const int leafThreshold) {
+template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
     uint32_t px, py;
     thread_pixel(px, py);
     const bool inside = px < static_cast<uint32_t>(p.width) && py < static_cast<uint32_t>(p.height);
@@ -47,7 +39,7 @@ __global__ void __launch_bounds__(256, 2) render_kernel_sm(const RenderParams p,
     float ix = 0, iy = 0, iz = 1;                           // 1 / d
     uint32_t nearBits = 0;                                  // bit a: d[a] < 0 -> the right child is nearer
     float tmin = 0, tmax = 0, best = 10000.0f, hbeta = 0, hgamma = 0;
-    uint32_t htri = 0xFFFFFFFFu, node = 0, li = 0, lend = 0;
+    uint32_t htri = 0xFFFFFFFFu, node = 0;
     int top = 0;
     uint2 stack[MCPT_KD_STACK];
     F3 thr = f3(1, 1, 1), cur = f3(0, 0, 0), acc = f3(0, 0, 0), acc2 = f3(0, 0, 0);
@@ -103,13 +95,7 @@ __global__ void __launch_bounds__(256, 2) render_kernel_sm(const RenderParams p,
     if (inside && s < sEnd) { start_sample(); begin_ray(); }
 
     while (true) {
-        const uint32_t mI = __ballot_sync(0xFFFFFFFFu, state == ST_INNER);
-        const uint32_t mL = __ballot_sync(0xFFFFFFFFu, state == ST_LEAF);
-        const uint32_t mS = __ballot_sync(0xFFFFFFFFu, state == ST_SHADE);
-        if ((mI | mL | mS) == 0u) break;
-        const int nI = __popc(mI), nL = __popc(mL), nS = __popc(mS);
-
-        if (nS >= shadeThreshold || (nI | nL) == 0) {
+        {
             // ================= SHADE: consume the hit, produce the next ray ====================
             if (state == ST_SHADE) {
                 bool done = false, haveRay = false;
@@ -205,25 +191,14 @@ __global__ void __launch_bounds__(256, 2) render_kernel_sm(const RenderParams p,
                 }
                 if (haveRay) begin_ray();
             }
-        } else if (nL >= leafThreshold || nI == 0) {
-            // ================= LEAF: one triangle test ==========================================
-            if (state == ST_LEAF) {
-                const uint32_t id = __ldg(p.sc.leaf_ids + li);
-                float t, be, ga;
-                if (tri_test(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
-                    best = t; htri = id; hbeta = be; hgamma = ga;
-                }
-                if (++li == lend) pop_or_finish();
-            }
-        } else {
-            // ================= INNER: one node step =============================================
+        }
+        if (__ballot_sync(0xFFFFFFFFu, state != ST_DEAD) == 0u) break;
+        // ================= TRAVERSE: one leaf visit per round, until enough lanes wait ==========
+        while (true) {
             if (state == ST_INNER) {
-                const uint2 n = __ldg(p.sc.kd_nodes + node);
-                const uint32_t axis = n.y & 3u;
-                if (axis == 3u) {
-                    li = n.x; lend = n.x + (n.y >> 2);
-                    if (li == lend) pop_or_finish(); else state = ST_LEAF;
-                } else {
+                uint2 n = __ldg(p.sc.kd_nodes + node);
+                while ((n.y & 3u) != 3u) {
+                    const uint32_t axis = n.y & 3u;
                     const float oa = axis == 0u ? ox : (axis == 1u ? oy : oz);
                     const float ia = axis == 0u ? ix : (axis == 1u ? iy : iz);
                     const float tp = (__uint_as_float(n.x) - oa) * ia;
@@ -239,8 +214,19 @@ __global__ void __launch_bounds__(256, 2) render_kernel_sm(const RenderParams p,
                         tmax = tp;
                         node = nearChild;
                     }
+                    n = __ldg(p.sc.kd_nodes + node);
                 }
+                const uint32_t lend = n.x + (n.y >> 2);
+                for (uint32_t li = n.x; li < lend; ++li) {
+                    const uint32_t id = __ldg(p.sc.leaf_ids + li);
+                    float t, be, ga;
+                    if (tri_test(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
+                        best = t; htri = id; hbeta = be; hgamma = ga;
+                    }
+                }
+                pop_or_finish();
             }
+            if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER)) >= shadeThreshold) break;
         }
     }
 
