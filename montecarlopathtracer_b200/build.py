@@ -57,6 +57,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         objs.append(o)
         if force or _newer(o, [os.path.join(CSRC, src)] + hdrs):
             cmd = [NVCC] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", o]
+            if os.environ.get("MCPT_TUNE"):       # tuning build: every render_kernel_sm variant (launch.cu)
+                cmd.insert(1, "-DMCPT_TUNE")
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             subprocess.check_call(cmd)

@@ -6,6 +6,16 @@
 #include "../../include/mcpt.h"
 #include "render_sm.cuh"
 
+#include <type_traits>
+
+// Shipping configuration of the persistent-lane kernel (profiles/r1_tuning.md).
+#ifndef MCPT_SM_VARIANT
+#define MCPT_SM_VARIANT 2
+#endif
+#ifndef MCPT_SM_MIN_BLOCKS
+#define MCPT_SM_MIN_BLOCKS 4
+#endif
+
 namespace mcpt {
 
 namespace {
@@ -111,9 +121,21 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
-    if (r.min_blocks >= 4) render_kernel_sm<RNG, NEE, MOMENTS, 4><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
-    else if (r.min_blocks == 3) render_kernel_sm<RNG, NEE, MOMENTS, 3><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
-    else render_kernel_sm<RNG, NEE, MOMENTS, 2><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
+#ifdef MCPT_TUNE
+    // tuning build: every kernel variant x residency for the headline combination (Philox, no NEE, no moments)
+    if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
+#define MCPT_V(MB, V) render_kernel_sm<RNG, NEE, MOMENTS, MB, V><<<grid, 256, 0, stream>>>(p, r.shade_threshold); break;
+#define MCPT_MB(V) switch (r.min_blocks) { case 4: MCPT_V(4, V) case 2: MCPT_V(2, V) default: MCPT_V(3, V) } break;
+        switch (r.variant & 7) {
+            case 0: MCPT_MB(0) case 1: MCPT_MB(1) case 2: MCPT_MB(2) case 3: MCPT_MB(3)
+            case 4: MCPT_MB(4) case 5: MCPT_MB(5) case 6: MCPT_MB(6) default: MCPT_MB(7)
+        }
+#undef MCPT_MB
+#undef MCPT_V
+        return cudaGetLastError();
+    }
+#endif
+    render_kernel_sm<RNG, NEE, MOMENTS, MCPT_SM_MIN_BLOCKS, MCPT_SM_VARIANT><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
     return cudaGetLastError();
 }
 

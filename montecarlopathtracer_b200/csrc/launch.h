@@ -23,7 +23,8 @@ struct RenderLaunch {
     bool kd, nee, moments;
     bool state_machine;    // render_kernel_sm (warp-voted state machine) instead of render_kernel
     int shade_threshold;   // lanes that must be waiting before the warp leaves the traverse phase
-    int min_blocks;        // 2, 3 or 4 resident 256-thread blocks per SM (register cap 128 / 85 / 64)
+    int min_blocks;        // tuning builds only: 2, 3 or 4 resident 256-thread blocks per SM (register cap 128 / 85 / 64)
+    int variant;           // tuning builds only: VAR bits of render_kernel_sm
 };
 
 // Number of kernels launched is returned through *launches (adds to it).
