@@ -23,6 +23,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(HERE, "liboracle.so")
 REF_SO = os.path.join(HERE, "_ref", "libmcpt_ref.so")
+REFCV_SO = os.path.join(HERE, "_ref", "libmcpt_refcv.so")
 REFERENCE_ROOT = "/root/reference"
 
 _vp = C.c_void_p
@@ -36,8 +37,9 @@ def build(force: bool = False) -> None:
     """Compile liboracle.so (always possible) and _ref (only where the reference is mounted)."""
     if force or not os.path.exists(ORACLE_SO) or _stale(ORACLE_SO):
         subprocess.check_call(["make", "-C", HERE, "liboracle.so"], stdout=subprocess.DEVNULL)
-    if os.path.isdir(REFERENCE_ROOT) and (force or not os.path.exists(REF_SO)
-                                          or os.path.getmtime(REF_SO) < os.path.getmtime(os.path.join(HERE, "ref_bridge.cpp"))):
+    if os.path.isdir(REFERENCE_ROOT) and (force or not os.path.exists(REF_SO) or not os.path.exists(REFCV_SO)
+                                          or os.path.getmtime(REF_SO) < os.path.getmtime(os.path.join(HERE, "ref_bridge.cpp"))
+                                          or os.path.getmtime(REFCV_SO) < os.path.getmtime(os.path.join(HERE, "ref_bridge_cv.cpp"))):
         subprocess.check_call(["make", "-C", HERE, "ref"], stdout=subprocess.DEVNULL)
 
 
@@ -195,6 +197,46 @@ class Reference:
 
     def free(self, handle):
         self.L.ref_scene_free(handle)
+
+
+class ReferenceCV:
+    """The CUDA tracer's own OBJ/MTL reader (CVMCTracer/.../Framework/ObjReader.cpp) and Matrix33f::det,
+    compiled in oracle/_ref/libmcpt_refcv.so (ref_bridge_cv.cpp)."""
+
+    def __init__(self):
+        if not os.path.exists(REFCV_SO):
+            raise FileNotFoundError(REFCV_SO)
+        L = C.CDLL(REFCV_SO)
+        L.refcv_load_obj.restype = _vp
+        L.refcv_load_obj.argtypes = [C.c_char_p]
+        L.refcv_free.argtypes = [_vp]
+        L.refcv_counts.argtypes = [_vp, _vp]
+        L.refcv_copy.argtypes = [_vp] * 5
+        L.refcv_det33.argtypes = [_vp]
+        L.refcv_det33.restype = C.c_float
+        self.L = L
+
+    @staticmethod
+    def available() -> bool:
+        return os.path.exists(REFCV_SO)
+
+    def load_obj(self, obj_path: str) -> SceneArrays:
+        """readObj + the table logic of CreateGeometry (CUTracer.cu:259-311)."""
+        h = self.L.refcv_load_obj(obj_path.encode())
+        if not h:
+            raise IOError("ObjModel::readObj failed for " + obj_path)
+        cnt = (C.c_int * 4)()
+        self.L.refcv_counts(h, cnt)
+        nV, nN, nT, nM = list(cnt)
+        s = SceneArrays(np.empty((nV, 3), np.float32), np.empty((nN, 3), np.float32),
+                        np.empty((nT, 7), np.uint32), np.empty((nM, 12), np.float32))
+        self.L.refcv_copy(h, _ptr(s.verts), _ptr(s.normals), _ptr(s.tris), _ptr(s.mats))
+        self.L.refcv_free(h)
+        return s
+
+    def det33(self, m) -> np.float32:
+        m = np.ascontiguousarray(m, np.float32).reshape(9)
+        return np.float32(self.L.refcv_det33(_ptr(m)))
 
 
 # --------------------------------------------------------------------------------------

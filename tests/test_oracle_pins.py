@@ -153,3 +153,41 @@ def test_render_is_deterministic_and_energy_bounded(oracle, scenes):
     a = oracle.cfg(32, 32, 2, 5)
     b = oracle.cfg(32, 32, 2, 5, sample_offset=2)
     assert np.allclose(sc.render(a)[0] + sc.render(b)[0], s1, rtol=0, atol=1e-12)
+
+
+def test_triangle_test_equals_the_cuda_twins_arithmetic_with_reference_det(oracle):
+    """The one explicit operation order the reference gives for the Cramer system is Matrix33f::det
+    (CVMCTracer/.../Framework/Math.hpp:169-175) applied to the matrices of CUTracer.cu:58-81.  The reference's
+    own det(), compiled in oracle/_ref/libmcpt_refcv.so, must give the oracle's t / beta / gamma bit for bit."""
+    from oracle.pyoracle import ReferenceCV, SceneArrays, TreeArrays
+    if not ReferenceCV.available():
+        pytest.skip("oracle/_ref/libmcpt_refcv.so not built")
+    cv = ReferenceCV()
+    g = np.random.default_rng(5)
+    f32 = np.float32
+    checked = 0
+    for _ in range(300):
+        tri = g.uniform(-3, 3, (3, 3)).astype(f32)
+        o = g.uniform(-3, 3, 3).astype(f32)
+        target = (tri[0] * f32(0.3) + tri[1] * f32(0.3) + tri[2] * f32(0.4)).astype(f32) + g.normal(0, 0.3, 3).astype(f32)
+        d = (target - o).astype(f32)
+        d = (d / np.linalg.norm(d)).astype(f32)
+        a, b, c = tri
+        col = lambda x, y, z: [x[0], y[0], z[0], x[1], y[1], z[1], x[2], y[2], z[2]]   # three column vectors, row-major
+        e1, e2, s = (a - b).astype(f32), (a - c).astype(f32), (a - o).astype(f32)
+        detA = cv.det33(col(e1, e2, d))
+        with np.errstate(all="ignore"):
+            beta = f32(cv.det33(col(s, e2, d)) / detA)
+            gamma = f32(cv.det33(col(e1, s, d)) / detA)
+            t = f32(cv.det33(col(e1, e2, s)) / detA)
+        hit = bool(f32(beta + gamma) < 1 and beta > 0 and gamma > 0 and t > 0 and t < 10000)
+        scene = SceneArrays(tri, np.array([[0, 1, 0]], f32), np.array([[0, 1, 2, 0, 0, 0, 0]], np.uint32), np.zeros((1, 12), f32))
+        box = np.array([[-10, -10, -10, 10, 10, 10]], f32)
+        one = TreeArrays(np.array([0xFFFFFFFF], np.uint32), np.array([0xFFFFFFFF], np.uint32), box, np.zeros(1, np.uint32),
+                         np.zeros(1, f32), np.zeros(1, np.uint32), np.array([1], np.uint32), np.arange(1, dtype=np.uint32), 0, 1)
+        otri, ot, ob, og, _ = oracle.scene(scene, one).intersect(np.concatenate([o, d])[None].astype(f32))
+        assert (otri[0] == 0) == hit
+        if hit:
+            assert (ot[0].view(np.uint32), ob[0].view(np.uint32), og[0].view(np.uint32)) == (t.view(np.uint32), beta.view(np.uint32), gamma.view(np.uint32))
+            checked += 1
+    assert checked > 50
