@@ -159,6 +159,11 @@ int mcpt_get_counters(mcpt_counters* out);
 /* Measured FP32 FMA issue rate of the bound device in GFLOP/s (roofline denominator for the
  * intersection / shading arithmetic; the reference publishes nothing comparable). */
 int mcpt_measure_fp32_peak(double* gflops);
+/* ---- image output (CUTracer.cu:383-396 step PNGs, GraphicsRTX.cpp:223-226 temp.png) ---------- */
+/* rgb: width*height*3 linear floats, top row first.  PNG stores clamp(pow(v, 1/gamma)) in 8 bits
+ * (gamma 2.2 = the display value of rtx.hlsl:402; 1.0 = the CUDA tracer's linear dump). */
+int mcpt_write_png(const char* path, const float* rgb, int width, int height, float gamma);
+int mcpt_write_pfm(const char* path, const float* rgb, int width, int height);
 const char* mcpt_last_error(void);
 const char* mcpt_version(void);
 

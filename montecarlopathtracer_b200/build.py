@@ -27,8 +27,8 @@ CXX = "/usr/bin/g++"
 CUDA_INC = "/usr/local/cuda/include"
 
 CU_SOURCES = ["launch.cu"]
-CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "obj_loader.cpp", "abi_geometry.cpp", "abi_render.cpp"]
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-fmad=false",
+CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "obj_loader.cpp", "image_io.cpp", "abi_geometry.cpp", "abi_render.cpp"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-diag-suppress=549",
               "-Xcompiler", "-fPIC", "-ccbin", CXX]
 CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-Wall", "-I" + CUDA_INC]
 
@@ -70,6 +70,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if force or _newer(LIB, objs):
         subprocess.check_call([NVCC, "-shared", "-ccbin", CXX, "-o", LIB] + objs +
                               ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp", "-Wno-deprecated-gpu-targets"])
+    cli_src = os.path.join(CSRC, "cli.cpp")
+    if force or _newer(CLI, [cli_src, LIB] + hdrs):   # headless driver, links only against the C ABI
+        subprocess.check_call([CXX, "-std=c++17", "-O2", cli_src, "-o", CLI, "-L" + LIBDIR, "-lmcpt", "-Wl,-rpath,$ORIGIN"])
     return LIB
 
 

@@ -87,6 +87,8 @@ def lib() -> C.CDLL:
     L.mcpt_get_counters.argtypes = [C.POINTER(Counters)]
     L.mcpt_traversal_stats.argtypes = [_vp, C.c_int64, C.c_int, _vp]
     L.mcpt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
+    L.mcpt_write_png.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int, C.c_float]
+    L.mcpt_write_pfm.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
     L.mcpt_last_error.restype = C.c_char_p
     L.mcpt_version.restype = C.c_char_p
     _lib = L
@@ -253,6 +255,19 @@ def measure_fp32_peak() -> float:
     g = C.c_double()
     _check(lib().mcpt_measure_fp32_peak(C.byref(g)))
     return g.value
+
+
+def write_png(path: str, rgb: np.ndarray, gamma: float = 2.2) -> None:
+    """8-bit PNG of clamp(rgb ** (1/gamma)); gamma 2.2 is the reference's display value (rtx.hlsl:402)."""
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    h, w, _ = rgb.shape
+    _check(lib().mcpt_write_png(path.encode(), _p(rgb), w, h, gamma))
+
+
+def write_pfm(path: str, rgb: np.ndarray) -> None:
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    h, w, _ = rgb.shape
+    _check(lib().mcpt_write_pfm(path.encode(), _p(rgb), w, h))
 
 
 def version() -> str:

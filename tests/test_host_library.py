@@ -109,3 +109,37 @@ def test_no_cpu_fallback(tracer, scenes):
             call()
         assert e.value.code == tracer.ERR_NO_DEVICE
     tracer.destroy_geometry()
+
+
+def test_image_writers(tracer, tmp_path):
+    """PNG = 8-bit clamp(v^(1/2.2)) (rtx.hlsl:402), decodable by any reader; PFM = raw floats, bottom row first."""
+    import struct, zlib
+    g = np.random.default_rng(0)
+    img = g.uniform(-0.1, 1.3, (37, 53, 3)).astype(np.float32)
+    p = str(tmp_path / "a.png")
+    tracer.write_png(p, img)
+    raw = open(p, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, hdr = 8, b"", None
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        assert zlib.crc32(typ + body) == struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0]
+        if typ == b"IHDR":
+            hdr = struct.unpack(">IIBBBBB", body)
+        if typ == b"IDAT":
+            idat += body
+        pos += 12 + n
+    assert hdr == (53, 37, 8, 2, 0, 0, 0)
+    px = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(37, 1 + 53 * 3)
+    assert (px[:, 0] == 0).all()
+    want = np.floor(np.clip(np.maximum(img, 0) ** (1 / 2.2), 0, 1) * 255 + 0.5)
+    assert np.abs(px[:, 1:].reshape(37, 53, 3).astype(int) - want.astype(int)).max() <= 1
+    q = str(tmp_path / "a.pfm")
+    tracer.write_pfm(q, img)
+    data = open(q, "rb").read()
+    head = b"PF\n53 37\n-1.0\n"
+    assert data.startswith(head)
+    assert np.array_equal(np.frombuffer(data[len(head):], np.float32).reshape(37, 53, 3)[::-1], img)
+    with pytest.raises(tracer.McptError):
+        tracer.write_png(str(tmp_path / "no_such_dir" / "x.png"), img)
