@@ -35,6 +35,8 @@ WORKLOADS = {
     "K2": ("scene01_lambert.mcpt", 1024, 1024, 1024, 8, 17.0, "Cornell Box 1024x1024, 1024 spp, depth 8, Lambert + area light"),
     "K3a": ("scene01.mcpt", 1024, 1024, 2048, 8, 17.0, "Cornell Box, mirror (Ns 1000) + glass (Tr 0.9) spheres, 1024x1024, 2048 spp, depth 8"),
     "K3b": ("scene02.mcpt", 1024, 1024, 2048, 8, 23.0, "scene02: 4 sphere lights + glossy Phong slabs, 1024x1024, 2048 spp, depth 8"),
+    "K4": ("heightfield:708", 1024, 1024, 256, 8, 17.0, "1 002 550-triangle height field in the Cornell shell, 1024x1024, 256 spp, depth 8"),
+    "K5": ("scene01_lambert.mcpt", 4096, 4096, 4096, 8, 17.0, "Cornell Box 4096x4096, 4096 spp (use --scaling strong to split the 4096 spp over the ranks), depth 8"),
 }
 
 # Algorithmic work per unit, counted from the reference's math:
@@ -44,7 +46,21 @@ F_TRI, B_TRI = 71, 40            # Cramer test: 68 flops + 3 divides; three floa
 
 def load_scene(name):
     from oracle.pyoracle import SceneArrays  # only used by the cpu_baseline / reference legs below
+    if name.startswith("heightfield:"):
+        from montecarlopathtracer_b200 import scenes
+        b = SceneArrays.load(os.path.join(ROOT, "scenes", "scene01_lambert.mcpt"))
+        return SceneArrays(*scenes.cornell_heightfield((b.verts, b.normals, b.tris, b.mats), int(name.split(":")[1])))
     return SceneArrays.load(os.path.join(ROOT, "scenes", name))
+
+
+def load_scene_gpu(T, name, build_mode):
+    """Product-side scene set-up for the GPU arm (no oracle code)."""
+    if name.startswith("heightfield:"):
+        from montecarlopathtracer_b200 import scenes
+        T.load_scene_file(os.path.join(ROOT, "scenes", "scene01_lambert.mcpt"), T.BUILD_SAH)
+        T.create_geometry(*scenes.cornell_heightfield(T.get_scene(), int(name.split(":")[1])), build_mode)
+    else:
+        T.load_scene_file(os.path.join(ROOT, "scenes", name), build_mode)
 
 
 class ClockSampler:
@@ -151,6 +167,8 @@ def main():
     ap.add_argument("--flags", default="", help="comma list: nee,ref_traversal")
     ap.add_argument("--tree", default="sah", choices=["sah", "reference"], help="KD builder for the render path (same hits either way)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank renders the workload's spp (default, the driver's contract); strong: the spp are split")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)
@@ -178,14 +196,17 @@ def main():
 
     T.initialize(local)
     build_mode = T.BUILD_REFERENCE if args.tree == "reference" else T.BUILD_SAH
-    T.load_scene_file(os.path.join(ROOT, "scenes", scene_file), build_mode)
+    load_scene_gpu(T, scene_file, build_mode)
     info = T.tree_info()
     v, n, tr, m = T.get_scene()   # host tables for the e2e leg
 
     stream = torch.cuda.current_stream()
     acc = torch.zeros(H, W, 4, device="cuda", dtype=torch.float32)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-    cfg = T.render_cfg(W, H, spp, depth, seed=0, sample_offset=rank * spp, flags=flags,
+    from montecarlopathtracer_b200 import multigpu as M
+    my_off, my_spp = M.rank_samples(rank, world, spp, args.scaling)
+    total_spp = spp * world if args.scaling == "weak" else spp
+    cfg = T.render_cfg(W, H, my_spp, depth, seed=0, sample_offset=my_off, flags=flags,
                        eye=(0, 5, eyez), at=(0, 5, eyez - 1))
 
     def barrier():
@@ -196,8 +217,7 @@ def main():
     def step():
         acc.zero_()
         T.render_accumulate_device(cfg, acc.data_ptr(), 0, stream.cuda_stream)
-        if dist is not None:
-            dist.reduce(acc, dst=0)   # the one exchange step of the path: NCCL sum over NVLink
+        M.reduce_accumulators(acc, dist)   # the one exchange step of the path: NCCL sum over NVLink
 
     for _ in range(max(args.warmup, 0)):
         step()
@@ -226,26 +246,38 @@ def main():
     else:
         rays_all, kms = float(rays), sum(kernel_ms)
     clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
-    paths_all = float(W) * H * spp * world * args.steps
+    paths_all = float(W) * H * total_spp * args.steps
     value = paths_all / (ms * 1e-3) / 1e6
     mrays = rays_all / (ms * 1e-3) / 1e6
 
     # ---- e2e: the reference-facing calls with HOST buffers, copies inside the timed region ----
     host = np.empty((H, W, 3), np.float32)
-    e2e_cfg = T.render_cfg(W, H, spp, depth, seed=0, sample_offset=rank * spp, flags=flags, eye=(0, 5, eyez), at=(0, 5, eyez - 1))
+    e2e_cfg = T.render_cfg(W, H, my_spp, depth, seed=0, sample_offset=my_off, flags=flags, eye=(0, 5, eyez), at=(0, 5, eyez - 1))
     e2e_steps = max(1, min(args.steps, 2))
-    T.create_geometry(v, n, tr, m, build_mode); T.render_scene(e2e_cfg, host)      # warm
+    pinned = torch.empty(H, W, 4, dtype=torch.float32).pin_memory() if world > 1 else None
+
+    def e2e_step():
+        T.create_geometry(v, n, tr, m, build_mode)     # CreateGeometry: host tables -> tree build -> H2D
+        if world == 1:
+            T.render_scene(e2e_cfg, host)              # RenderScene: kernel -> mean -> D2H of the image
+        else:                                          # N ranks: render share -> one NCCL reduce -> D2H on rank 0
+            acc.zero_()
+            T.render_accumulate_device(e2e_cfg, acc.data_ptr(), 0, stream.cuda_stream)
+            M.reduce_accumulators(acc, dist)
+            if rank == 0:
+                pinned.copy_(acc, non_blocking=False)
+                host[...] = M.finalize(pinned)
+
+    e2e_step()      # warm
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        T.create_geometry(v, n, tr, m, build_mode)     # CreateGeometry: host tables -> tree -> H2D
-        T.render_scene(e2e_cfg, host)      # RenderScene: kernel -> D2H of the image
-        launches_e2e = T.counters().launches
+        e2e_step()
     torch.cuda.synchronize()
     e2e_s = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
     if dist is not None:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    e2e_value = float(W) * H * spp * world * e2e_steps / e2e_s.item() / 1e6
+    e2e_value = float(W) * H * total_spp * e2e_steps / e2e_s.item() / 1e6
 
     if rank != 0:
         if dist is not None:
@@ -254,17 +286,18 @@ def main():
 
     # ---- roofline of the dominant kernel (render_kernel), per launch ----
     line = {"metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "mrays_per_s": mrays, "rays_per_path": rays_all / paths_all,
             "config": {"workload": desc + ("" if not args.spp else f" [spp overridden to {spp}]"),
-                       "spp_per_gpu": spp, "parallelism": f"spp-split x{world}, one NCCL reduce" if world > 1 else "1 GPU",
+                       "spp_per_gpu": my_spp, "spp_total": total_spp, "parallelism": f"spp-split x{world}, one NCCL reduce" if world > 1 else "1 GPU",
                        "estimator": "NEE" if flags & T.FLAG_NEE else "emission-on-hit (reference)", "rng": "philox4x32-10",
                        "l2": "flushed between timed steps (256 MiB memset); scene is L1/L2-resident by design",
                        "tree": "own SAH builder (MCPT_BUILD_SAH)" if build_mode == T.BUILD_SAH else "reference-rule tree (MCPT_BUILD_REFERENCE)",
                        "tree_nodes": info.num_nodes, "scene_bytes_hbm": int(info.device_bytes)},
             "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": int(info.device_bytes),
-                    "d2h_bytes_per_step": W * H * 3 * 4, "steps": e2e_steps},
+                    "d2h_bytes_per_step": W * H * (3 if world == 1 else 4) * 4, "steps": e2e_steps,
+                    "includes": "mcpt_create_geometry (host KD build + H2D) and the image D2H every step"},
             "gpu_launches": int(launches), "clocks": clocks}
 
     cpu = None

@@ -263,3 +263,32 @@ def test_sah_tree_renders_the_same_image(gpu, scenes):
         _load(T, s, mode)
         imgs.append(T.render_scene(T.render_cfg(128, 96, 6, 5, seed=2)))
     assert np.isclose(imgs[0], imgs[1], rtol=1e-4, atol=1e-6).all(-1).mean() > 0.999
+
+
+def test_tessellated_surface_scene(gpu, oracle, scenes):
+    """K4-style scene at test size (8 214 triangles in the Cornell shell): both traversals find the oracle's hits,
+    both tree builders render the oracle's image on the shared Philox stream."""
+    from montecarlopathtracer_b200 import scenes as S
+    from oracle.pyoracle import SceneArrays
+    T, b = gpu, scenes["scene01_lambert"]
+    s = SceneArrays(*S.cornell_heightfield((b.verts, b.normals, b.tris, b.mats), 64))
+    assert len(s.tris) == 22 + 2 * 64 * 64
+    osc = oracle.scene(s)
+    rays = np.concatenate([oracle.primary_rays(oracle.cfg(256, 256, 1, 8, jitter=0)), _random_rays(s, 1 << 17, seed=4)])
+    tri, t, bb, gg, _ = osc.intersect(rays)
+    assert (tri >= 22).mean() > 0.2
+    W, H, spp = 96, 96, 4
+    osum, _, _, ocnt = osc.render(oracle.cfg(W, H, spp, 8, rng_mode=1, seed=6))
+    for mode in (T.BUILD_REFERENCE, T.BUILD_SAH):
+        _load(T, s, mode)
+        if mode == T.BUILD_REFERENCE:
+            rtri, rt, _, _ = T.intersect_batch(rays, T.ISECT_REFERENCE)
+            assert np.array_equal(rtri, tri) and np.array_equal(_bits(rt)[tri >= 0], _bits(t)[tri >= 0])
+        ktri, kt, _, _ = T.intersect_batch(rays, T.ISECT_KD)
+        bad = np.flatnonzero((ktri != tri) | ((tri >= 0) & (_bits(kt) != _bits(t))))
+        assert len(bad) <= 1e-4 * len(rays), len(bad)
+        if len(bad):
+            btri, bt, _, _, _ = _brute_force(oracle, s, rays[bad])
+            assert np.array_equal(btri, ktri[bad]) and np.array_equal(_bits(bt), _bits(kt[bad]))
+        mean = T.render_scene(T.render_cfg(W, H, spp, 8, seed=6))
+        assert np.isclose(mean, osum / spp, rtol=1e-3, atol=1e-5).all(-1).mean() > 0.97

@@ -1,0 +1,63 @@
+"""N > 1 host logic on CPU: world_size-2 gloo.  Each rank fills its accumulation buffer with ITS sample range
+(the CPU oracle stands in for the GPU kernel here -- tests only), one reduce combines them, and rank 0 must hold
+exactly the single-rank render of the whole range."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from conftest import ROOT, SCENES
+
+
+def _worker(rank, world, port, scaling, spp, out_path):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from montecarlopathtracer_b200 import multigpu as M
+        from oracle.pyoracle import Oracle, SceneArrays
+        o = Oracle()
+        sc = o.scene(SceneArrays.load(os.path.join(SCENES, "scene01_lambert.mcpt")))
+        W, H = 40, 24
+        off, n = M.rank_samples(rank, world, spp, scaling)
+        acc = torch.zeros(H, W, 4, dtype=torch.float32)
+        if n:
+            s, _, _, _ = sc.render(o.cfg(W, H, n, 8, rng_mode=1, seed=3, sample_offset=off, threads=2))
+            acc[..., :3] = torch.from_numpy(s.astype(np.float32))
+            acc[..., 3] = n
+        M.reduce_accumulators(acc, dist)
+        if rank == 0:
+            np.save(out_path, np.concatenate([M.finalize(acc), acc[..., 3:].numpy()], -1))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("scaling,spp", [("weak", 3), ("strong", 7), ("strong", 1)])
+def test_two_ranks_equal_one_rank(oracle, scenes, tmp_path, scaling, spp):
+    out = str(tmp_path / "img.npy")
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_worker, args=(2, port, scaling, spp, out), nprocs=2, join=True)
+    got = np.load(out)
+    total = spp * 2 if scaling == "weak" else spp
+    assert (got[..., 3] == total).all()
+    s, _, _, _ = oracle.scene(scenes["scene01_lambert"]).render(oracle.cfg(40, 24, total, 8, rng_mode=1, seed=3))
+    assert np.allclose(got[..., :3], s / total, rtol=1e-5, atol=1e-6)   # fp32 reassociation only
+
+
+def test_split_samples_partitions_exactly():
+    from montecarlopathtracer_b200 import multigpu as M
+    for total in (0, 1, 7, 1024, 4096, 4097):
+        for world in (1, 2, 3, 4, 8):
+            parts = M.split_samples(total, world)
+            assert len(parts) == world and parts[0][0] == 0
+            assert all(a[0] + a[1] == b[0] for a, b in zip(parts, parts[1:]))
+            assert parts[-1][0] + parts[-1][1] == total
+            assert max(n for _, n in parts) - min(n for _, n in parts) <= 1
+    assert M.rank_samples(3, 8, 1024, "weak") == (3072, 1024)
+    assert M.rank_samples(3, 8, 4096, "strong") == (1536, 512)
+    with pytest.raises(ValueError):
+        M.rank_samples(2, 2, 4)
