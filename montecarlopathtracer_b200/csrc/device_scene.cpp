@@ -53,7 +53,7 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         const float e2[3] = {a[0] - c[0], a[1] - c[1], a[2] - c[2]};
         const float c3 = e1[1] * e2[2] - e2[1] * e1[2];
         out.tri_isect[3 * t] = make_float4(a[0], a[1], a[2], c3);
-        out.tri_isect[3 * t + 1] = make_float4(e1[0], e1[1], e1[2], 0.0f);
+        out.tri_isect[3 * t + 1] = make_float4(e1[0], e1[1], e1[2], as_float(static_cast<uint32_t>(t)));
         out.tri_isect[3 * t + 2] = make_float4(e2[0], e2[1], e2[2], 0.0f);
         const float* n0 = &scene.normals[3 * static_cast<size_t>(r[3])];
         const float* n1 = &scene.normals[3 * static_cast<size_t>(r[4])];
@@ -75,6 +75,10 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
             out.emitters.push_back(make_float4(static_cast<float>(v[0]), static_cast<float>(v[1]), static_cast<float>(v[2]), as_float(static_cast<uint32_t>(t))));
         }
     }
+    out.leaf_tris.resize(3 * out.leaf_ids.size());
+    for (size_t k = 0; k < out.leaf_ids.size(); ++k)
+        for (int j = 0; j < 3; ++j) out.leaf_tris[3 * k + j] = out.tri_isect[3 * static_cast<size_t>(out.leaf_ids[k]) + j];
+
     // running CDF over emitter area for area-uniform light sampling
     double run = 0.0;
     for (size_t i = 0; i < areas.size(); ++i) {

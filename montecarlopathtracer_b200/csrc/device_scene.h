@@ -15,6 +15,9 @@
 //   tri_isect  3 x float4 per triangle {a.xyz, c3} {e1.xyz, 0} {e2.xyz, 0}
 //                 e1 = a-b, e2 = a-c (the ray-independent columns of rtx.hlsl:167-186),
 //                 c3 = e1.y*e2.z - e2.y*e1.z (the one ray-independent cofactor)
+//   leaf_tris  3 x float4 per LEAF REFERENCE: the tri_isect record of leaf_ids[k] copied in place k, with the
+//                 triangle id in the free lane {e1.xyz, id bits}: a leaf's triangles are consecutive 48-byte
+//                 records and the render path needs no id -> record indirection (tuning build variant)
 //   tri_shade  3 x float4 per triangle {n0.xyz, matId bits} {n1.xyz, 0} {n2.xyz, 0}
 //   mats       3 x float4 per material {Ka, Ns} {Kd, Tr} {Ks, Ni}
 //   emitters   3 x float4 per emitting triangle {a.xyz, area} {b-a, cdf} {c-a, triangle id bits}
@@ -33,6 +36,7 @@ struct DScene {
     const uint2* kd_nodes;
     const uint32_t* leaf_ids;
     const float4* tri_isect;
+    const float4* leaf_tris;
     const float4* tri_shade;
     const float4* mats;
     const float4* emitters;
@@ -52,12 +56,12 @@ struct PackedScene {
     std::vector<float4> ref_nodes;
     std::vector<uint2> kd_nodes;
     std::vector<uint32_t> leaf_ids;
-    std::vector<float4> tri_isect, tri_shade, mats, emitters;
+    std::vector<float4> tri_isect, leaf_tris, tri_shade, mats, emitters;
     float bmin[3], bmax[3];
     float emitter_area = 0.0f;
     size_t bytes() const {
         return ref_nodes.size() * 16 + kd_nodes.size() * 8 + leaf_ids.size() * 4 +
-               (tri_isect.size() + tri_shade.size() + mats.size() + emitters.size()) * 16;
+               (tri_isect.size() + leaf_tris.size() + tri_shade.size() + mats.size() + emitters.size()) * 16;
     }
 };
 

@@ -17,6 +17,7 @@
 #include <chrono>
 #include <cmath>
 #include <cfloat>
+#include <cstdlib>
 
 #include "host_scene.h"
 
@@ -40,9 +41,14 @@ struct Node {
     std::vector<uint32_t> ids;
 };
 
+float env_float(const char* name, float dflt) {
+    const char* v = std::getenv(name);
+    return v && *v ? static_cast<float>(std::atof(v)) : dflt;
+}
 const float kTraversalCost = 1.0f;
-const float kIntersectCost = 2.5f;   // the strict Cramer test + its three dependent loads vs one plane step
-const float kEmptyBonus = 0.8f;
+// the strict Cramer test + its loads against one plane step; defaults from profiles/r1_tuning.md
+const float kIntersectCost = env_float("MCPT_SAH_CI", 1.0f);
+const float kEmptyBonus = env_float("MCPT_SAH_EB", 1.0f);
 
 inline float surface(const Box& b) {
     const float x = b.hi[0] - b.lo[0], y = b.hi[1] - b.lo[1], z = b.hi[2] - b.lo[2];

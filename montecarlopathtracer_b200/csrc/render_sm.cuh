@@ -20,13 +20,13 @@ namespace mcpt {
 
 enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 
-// VAR bit 0: a new ray descends to its first leaf inside the SHADE phase (all shading lanes start at the
-//            root together), so a TRAVERSE round is [test leaf, pop, short descent to the next leaf];
-// VAR bit 1: predicated (branch-free) node step;
-// VAR bit 2: tri_test<true> (division-free rejections, intersect.cuh).
+// VAR (tuning knobs, profiles/r1_tuning.md):
+//   bit 0  leaf triangles are read as consecutive records from leaf_tris (no id -> record indirection);
+//   bit 1  empty leaves are popped inside the descent loop instead of costing a whole TRAVERSE round;
+//   bit 2  tri_test<true> (division-free rejections, intersect.cuh).
 template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR>
 __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
-    constexpr bool EARLY = (VAR & 1) != 0, FLAT = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0;
+    constexpr bool LEAFREC = (VAR & 1) != 0, SKIPEMPTY = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0;
     uint32_t px, py;
     thread_pixel(px, py);
     const bool inside = px < static_cast<uint32_t>(p.width) && py < static_cast<uint32_t>(p.height);
@@ -97,13 +97,15 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
         }
     };
 
-    // From `node` down to the first leaf the ray enters within [tmin, tmax]; far children that the ray
-    // also crosses are pushed with the interval end they inherit.  Leaves [li, lend) pending.
+    // From `node` down to the next leaf the ray enters within [tmin, tmax]; far children that the ray
+    // also crosses are pushed with the interval end they inherit.  The node step is predicated (no
+    // divergent branch): 28 SASS instructions.  Leaves [li, lend) pending on return (state ST_INNER),
+    // or the ray is finished (state ST_SHADE) when SKIPEMPTY ran off the last empty leaf.
     auto descend = [&]() {
-        uint2 n = __ldg(p.sc.kd_nodes + node);
-        while ((n.y & 3u) != 3u) {
-            const uint32_t axis = n.y & 3u;
-            if (FLAT) {
+        while (true) {
+            uint2 n = __ldg(p.sc.kd_nodes + node);
+            while ((n.y & 3u) != 3u) {
+                const uint32_t axis = n.y & 3u;
                 float oa = oz, ia = iz;
                 if (axis == 0u) { oa = ox; ia = ix; }
                 if (axis == 1u) { oa = oy; ia = iy; }
@@ -117,40 +119,33 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                     tmax = tp;
                 }
                 node = (farOnly && !nearOnly) ? farChild : nearChild;
-            } else {
-                const float oa = axis == 0u ? ox : (axis == 1u ? oy : oz);
-                const float ia = axis == 0u ? ix : (axis == 1u ? iy : iz);
-                const float tp = (__uint_as_float(n.x) - oa) * ia;
-                const uint32_t nb = (nearBits >> axis) & 1u, left = n.y >> 2;
-                const uint32_t nearChild = left + nb, farChild = left + (nb ^ 1u);
-                if (tp > tmax) {
-                    node = nearChild;
-                } else if (tp < tmin) {
-                    node = farChild;
-                } else {
-                    stack[top] = make_uint2(farChild, __float_as_uint(tmax));
-                    ++top;
-                    tmax = tp;
-                    node = nearChild;
-                }
+                n = __ldg(p.sc.kd_nodes + node);
             }
-            n = __ldg(p.sc.kd_nodes + node);
+            li = n.x; lend = n.x + (n.y >> 2);
+            if (!SKIPEMPTY || li != lend) break;
+            pop_or_finish();
+            if (state != ST_INNER) break;
         }
-        li = n.x; lend = n.x + (n.y >> 2);
     };
     auto test_leaf = [&]() {
         for (; li < lend; ++li) {
-            const uint32_t id = __ldg(p.sc.leaf_ids + li);
             float t, be, ga;
-            if (tri_test<FASTREJ>(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
-                best = t; htri = id; hbeta = be; hgamma = ga;
+            if (LEAFREC) {
+                uint32_t id;
+                if (tri_test<FASTREJ>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, &id)) {
+                    best = t; htri = id; hbeta = be; hgamma = ga;
+                }
+            } else {
+                const uint32_t id = __ldg(p.sc.leaf_ids + li);
+                if (tri_test<FASTREJ>(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
+                    best = t; htri = id; hbeta = be; hgamma = ga;
+                }
             }
         }
     };
 
     if (inside && s < sEnd) {
         start_sample(); begin_ray();
-        if (EARLY && state == ST_INNER) { descend(); state = ST_LEAF; }
     }
 
     while (true) {
@@ -248,32 +243,20 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                     ++s;
                     if (s < sEnd) { start_sample(); haveRay = true; } else state = ST_DEAD;
                 }
-                if (haveRay) {
-                    begin_ray();
-                    if (EARLY && state == ST_INNER) { descend(); state = ST_LEAF; }
-                }
+                if (haveRay) begin_ray();
             }
         }
         if (__ballot_sync(0xFFFFFFFFu, state != ST_DEAD) == 0u) break;
         // ================= TRAVERSE: one leaf visit per round, until enough lanes wait ==========
-        if (EARLY) {
-            while (true) {
-                if (state == ST_LEAF) {
-                    test_leaf();
-                    pop_or_finish();
-                    if (state == ST_INNER) { descend(); state = ST_LEAF; }
-                }
-                if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_LEAF)) >= shadeThreshold) break;
-            }
-        } else {
-            while (true) {
-                if (state == ST_INNER) {
-                    descend();
+        while (true) {
+            if (state == ST_INNER) {
+                descend();
+                if (!SKIPEMPTY || state == ST_INNER) {
                     test_leaf();
                     pop_or_finish();
                 }
-                if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER)) >= shadeThreshold) break;
             }
+            if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER)) >= shadeThreshold) break;
         }
     }
 
