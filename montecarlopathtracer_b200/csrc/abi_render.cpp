@@ -2,6 +2,7 @@
 // Replaces PW::Tracer::RenderScene (CUTracer.cu:340-404) and the per-frame part of
 // GraphicsRTX::DoOnUpdate (GraphicsRTX.cpp:173-209): camera, frame seeds, launch, read-back.
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <random>
@@ -54,8 +55,8 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     cudaError_t e;
     if ((e = c.d_slices.ensure(pixels * chunks)) != cudaSuccess) return fail_cuda(e, "alloc slices");
     if (moments && (e = c.d_slices_sq.ensure(pixels * chunks)) != cudaSuccess) return fail_cuda(e, "alloc slices_sq");
-    if ((e = c.d_counter.ensure(4)) != cudaSuccess) return fail_cuda(e, "alloc counter");
-    if ((e = cudaMemsetAsync(c.d_counter.ptr, 0, sizeof(unsigned long long), stream)) != cudaSuccess) return fail_cuda(e, "memset");
+    if ((e = c.d_counter.ensure(16)) != cudaSuccess) return fail_cuda(e, "alloc counter");
+    if ((e = cudaMemsetAsync(c.d_counter.ptr, 0, 16 * sizeof(unsigned long long), stream)) != cudaSuccess) return fail_cuda(e, "memset");
 
     RenderLaunch r;
     r.sc = c.dscene;
@@ -122,14 +123,20 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
 int finish_counters(cudaStream_t stream) {
     Context& c = ctx();
     cudaError_t e;
-    unsigned long long rays = 0;
-    if ((e = cudaMemcpyAsync(&rays, c.d_counter.ptr, sizeof(rays), cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return fail_cuda(e, "counter readback");
+    unsigned long long cnt[16] = {0};
+    if ((e = cudaMemcpyAsync(cnt, c.d_counter.ptr, sizeof(cnt), cudaMemcpyDeviceToHost, stream)) != cudaSuccess) return fail_cuda(e, "counter readback");
     cudaEventRecord(c.ev[2], stream);
     if ((e = cudaStreamSynchronize(stream)) != cudaSuccess) return fail_cuda(e, "render");
     float k = 0, t = 0;
     cudaEventElapsedTime(&k, c.ev[0], c.ev[1]);
     cudaEventElapsedTime(&t, c.ev[0], c.ev[2]);
+    const unsigned long long rays = cnt[0];
     c.counters.rays = rays;
+    if (cnt[1] && std::getenv("MCPT_SM_STATS")) {  // tuning builds, VAR bit 3
+        std::fprintf(stderr, "rounds %llu lanes/round %.2f | node steps: mean/lane %.2f max %.2f | tri tests: mean/lane %.2f max %.2f | shade phases %llu lanes/phase %.2f done/phase %.2f | rounds/phase %.2f\n",
+                     cnt[1], double(cnt[2]) / cnt[1], double(cnt[3]) / cnt[2], double(cnt[4]) / cnt[1], double(cnt[5]) / cnt[2], double(cnt[6]) / cnt[1],
+                     cnt[7], double(cnt[8]) / cnt[7], double(cnt[9]) / cnt[7], double(cnt[1]) / cnt[7]);
+    }
     c.counters.kernel_ms = k;
     c.counters.total_ms = t;
     return MCPT_OK;

@@ -126,6 +126,7 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
 #define MCPT_V(MB, V) render_kernel_sm<RNG, NEE, MOMENTS, MB, V><<<grid, 256, 0, stream>>>(p, r.shade_threshold); break;
 #define MCPT_MB(V) switch (r.min_blocks) { case 5: MCPT_V(5, V) case 3: MCPT_V(3, V) default: MCPT_V(4, V) } break;
+        if (r.variant & 8) { render_kernel_sm<RNG, NEE, MOMENTS, 4, 13><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
         switch (r.variant & 7) {
             case 0: MCPT_MB(0) case 1: MCPT_MB(1) case 2: MCPT_MB(2) case 3: MCPT_MB(3)
             case 4: MCPT_MB(4) case 5: MCPT_MB(5) case 6: MCPT_MB(6) default: MCPT_MB(7)

@@ -22,11 +22,12 @@ enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 
 // VAR (tuning knobs, profiles/r1_tuning.md):
 //   bit 0  leaf triangles are read as consecutive records from leaf_tris (no id -> record indirection);
-//   bit 1  empty leaves are popped inside the descent loop instead of costing a whole TRAVERSE round;
+//   bit 1  tri_test_flat: no early exits, one combined rejection in front of the divides (needs bit 0);
 //   bit 2  tri_test<true> (division-free rejections, intersect.cuh).
 template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR>
 __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
-    constexpr bool LEAFREC = (VAR & 1) != 0, SKIPEMPTY = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0;
+    constexpr bool LEAFREC = (VAR & 1) != 0, FLATTRI = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0;
+    uint32_t st[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
     uint32_t px, py;
     thread_pixel(px, py);
     const bool inside = px < static_cast<uint32_t>(p.width) && py < static_cast<uint32_t>(p.height);
@@ -99,38 +100,40 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
 
     // From `node` down to the next leaf the ray enters within [tmin, tmax]; far children that the ray
     // also crosses are pushed with the interval end they inherit.  The node step is predicated (no
-    // divergent branch): 28 SASS instructions.  Leaves [li, lend) pending on return (state ST_INNER),
-    // or the ray is finished (state ST_SHADE) when SKIPEMPTY ran off the last empty leaf.
+    // divergent branch): 28 SASS instructions.  Leaf triangles [li, lend) pending on return.
+    uint32_t myNodes = 0, myTris = 0;
     auto descend = [&]() {
-        while (true) {
-            uint2 n = __ldg(p.sc.kd_nodes + node);
-            while ((n.y & 3u) != 3u) {
-                const uint32_t axis = n.y & 3u;
-                float oa = oz, ia = iz;
-                if (axis == 0u) { oa = ox; ia = ix; }
-                if (axis == 1u) { oa = oy; ia = iy; }
-                const float tp = (__uint_as_float(n.x) - oa) * ia;
-                const uint32_t nb = (nearBits >> axis) & 1u, left = n.y >> 2;
-                const uint32_t nearChild = left + nb, farChild = left + (nb ^ 1u);
-                const bool nearOnly = tp > tmax, farOnly = tp < tmin;
-                if (!(nearOnly || farOnly)) {
-                    stack[top] = make_uint2(farChild, __float_as_uint(tmax));
-                    ++top;
-                    tmax = tp;
-                }
-                node = (farOnly && !nearOnly) ? farChild : nearChild;
-                n = __ldg(p.sc.kd_nodes + node);
+        uint2 n = __ldg(p.sc.kd_nodes + node);
+        while ((n.y & 3u) != 3u) {
+            if (STATS) ++myNodes;
+            const uint32_t axis = n.y & 3u;
+            float oa = oz, ia = iz;
+            if (axis == 0u) { oa = ox; ia = ix; }
+            if (axis == 1u) { oa = oy; ia = iy; }
+            const float tp = (__uint_as_float(n.x) - oa) * ia;
+            const uint32_t nb = (nearBits >> axis) & 1u, left = n.y >> 2;
+            const uint32_t nearChild = left + nb, farChild = left + (nb ^ 1u);
+            const bool nearOnly = tp > tmax, farOnly = tp < tmin;
+            if (!(nearOnly || farOnly)) {
+                stack[top] = make_uint2(farChild, __float_as_uint(tmax));
+                ++top;
+                tmax = tp;
             }
-            li = n.x; lend = n.x + (n.y >> 2);
-            if (!SKIPEMPTY || li != lend) break;
-            pop_or_finish();
-            if (state != ST_INNER) break;
+            node = (farOnly && !nearOnly) ? farChild : nearChild;
+            n = __ldg(p.sc.kd_nodes + node);
         }
+        li = n.x; lend = n.x + (n.y >> 2);
     };
     auto test_leaf = [&]() {
         for (; li < lend; ++li) {
             float t, be, ga;
-            if (LEAFREC) {
+            if (STATS) ++myTris;
+            if (LEAFREC && FLATTRI) {
+                uint32_t id;
+                if (tri_test_flat(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, id)) {
+                    best = t; htri = id; hbeta = be; hgamma = ga;
+                }
+            } else if (LEAFREC) {
                 uint32_t id;
                 if (tri_test<FASTREJ>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, &id)) {
                     best = t; htri = id; hbeta = be; hgamma = ga;
@@ -151,6 +154,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
     while (true) {
         {
             // ================= SHADE: consume the hit, produce the next ray ====================
+            if (STATS) { st[7] += 1; st[8] += __popc(__ballot_sync(0xFFFFFFFFu, state == ST_SHADE)); }
             if (state == ST_SHADE) {
                 bool done = false, haveRay = false;
                 if (NEE && shadow) {
@@ -237,6 +241,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                         }
                     }
                 }
+                if (STATS && done) st[9] += 1;
                 if (done) {
                     acc = acc + cur;
                     if (MOMENTS) acc2 = acc2 + cur * cur;
@@ -249,12 +254,15 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
         if (__ballot_sync(0xFFFFFFFFu, state != ST_DEAD) == 0u) break;
         // ================= TRAVERSE: one leaf visit per round, until enough lanes wait ==========
         while (true) {
+            if (STATS) { myNodes = 0; myTris = 0; st[1] += 1; st[2] += __popc(__ballot_sync(0xFFFFFFFFu, state == ST_INNER)); }
             if (state == ST_INNER) {
                 descend();
-                if (!SKIPEMPTY || state == ST_INNER) {
-                    test_leaf();
-                    pop_or_finish();
-                }
+                test_leaf();
+                pop_or_finish();
+            }
+            if (STATS) {
+                st[3] += __reduce_add_sync(0xFFFFFFFFu, myNodes); st[4] += __reduce_max_sync(0xFFFFFFFFu, myNodes);
+                st[5] += __reduce_add_sync(0xFFFFFFFFu, myTris); st[6] += __reduce_max_sync(0xFFFFFFFFu, myTris);
             }
             if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER)) >= shadeThreshold) break;
         }
@@ -264,6 +272,11 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
         const size_t o = (static_cast<size_t>(chunk) * p.height + py) * p.width + px;
         p.sum[o] = make_float4(acc.x, acc.y, acc.z, static_cast<float>(localN));
         if (MOMENTS) p.sumsq[o] = make_float4(acc2.x, acc2.y, acc2.z, static_cast<float>(localN));
+    }
+    if (STATS) {
+        st[9] = __reduce_add_sync(0xFFFFFFFFu, st[9]);
+        if ((threadIdx.x & 31u) == 0u)
+            for (int k = 1; k < 10; ++k) atomicAdd(p.ray_counter + k, static_cast<unsigned long long>(st[k]));
     }
     for (int off = 16; off > 0; off >>= 1) nrays += __shfl_xor_sync(0xFFFFFFFFu, nrays, off);
     if ((threadIdx.x & 31u) == 0u && nrays) atomicAdd(p.ray_counter, static_cast<unsigned long long>(nrays));
