@@ -64,7 +64,8 @@ enum {
 /* Intersection kernels selectable through mcpt_intersect_batch. */
 enum {
     MCPT_ISECT_REFERENCE = 0, /* rtx.hlsl:144-211 visit order and slab test, strict IEEE arithmetic */
-    MCPT_ISECT_KD = 1         /* front-to-back plane traversal of the compact KD nodes (render path)  */
+    MCPT_ISECT_KD = 1,        /* front-to-back plane traversal of the compact KD nodes with a stack   */
+    MCPT_ISECT_ROPES = 2      /* stackless leaf-to-leaf traversal over neighbour links (render path)  */
 };
 
 /* Flat scene tables: exactly the fields of CSTriangle / CSMaterial (Structure.hpp:196-211) and

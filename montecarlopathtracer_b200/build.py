@@ -27,7 +27,7 @@ CXX = "/usr/bin/g++"
 CUDA_INC = "/usr/local/cuda/include"
 
 CU_SOURCES = ["launch.cu"]
-CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "obj_loader.cpp", "image_io.cpp", "abi_geometry.cpp", "abi_render.cpp"]
+CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "kd_ropes.cpp", "obj_loader.cpp", "image_io.cpp", "abi_geometry.cpp", "abi_render.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-diag-suppress=549",
               "-Xcompiler", "-fPIC", "-ccbin", CXX]
 CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-Wall", "-I" + CUDA_INC]

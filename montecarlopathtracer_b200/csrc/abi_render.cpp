@@ -77,7 +77,8 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.state_machine = (cfg->flags & MCPT_FLAG_SIMPLE_KERNEL) == 0;
     r.shade_threshold = env_int("MCPT_SM_SHADE", 20);      // tuning knobs, defaults from profiles/r1_tuning.md
     r.min_blocks = env_int("MCPT_SM_MINBLOCKS", 4);
-    r.variant = env_int("MCPT_SM_VARIANT", 5);
+    r.variant = env_int("MCPT_SM_VARIANT", 23);
+    r.cam_threshold = env_int("MCPT_SM_CAMR", 16);
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
         // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))
         // per frame, i.e. the raw generator output.
@@ -133,9 +134,9 @@ int finish_counters(cudaStream_t stream) {
     const unsigned long long rays = cnt[0];
     c.counters.rays = rays;
     if (cnt[1] && std::getenv("MCPT_SM_STATS")) {  // tuning builds, VAR bit 3
-        std::fprintf(stderr, "rounds %llu lanes/round %.2f | node steps: mean/lane %.2f max %.2f | tri tests: mean/lane %.2f max %.2f | shade phases %llu lanes/phase %.2f done/phase %.2f | rounds/phase %.2f\n",
+        std::fprintf(stderr, "rounds %llu lanes/round %.2f | node steps: mean/lane %.2f max %.2f | tri tests: mean/lane %.2f max %.2f | shade phases %llu lanes/phase %.2f done/phase %.2f | rounds/phase %.2f | raw3 %llu raw4 %llu\n",
                      cnt[1], double(cnt[2]) / cnt[1], double(cnt[3]) / cnt[2], double(cnt[4]) / cnt[1], double(cnt[5]) / cnt[2], double(cnt[6]) / cnt[1],
-                     cnt[7], double(cnt[8]) / cnt[7], double(cnt[9]) / cnt[7], double(cnt[1]) / cnt[7]);
+                     cnt[7], double(cnt[8]) / cnt[7], double(cnt[9]) / cnt[7], double(cnt[1]) / cnt[7], cnt[3], cnt[4]);
     }
     c.counters.kernel_ms = k;
     c.counters.total_ms = t;
@@ -194,7 +195,7 @@ int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, vo
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (n < 0 || (n > 0 && (!dev_rays || !dev_tri))) return fail(MCPT_ERR_INVALID, "bad ray batch");
-    if (variant != MCPT_ISECT_REFERENCE && variant != MCPT_ISECT_KD) return fail(MCPT_ERR_INVALID, "unknown variant");
+    if (variant != MCPT_ISECT_REFERENCE && variant != MCPT_ISECT_KD && variant != MCPT_ISECT_ROPES) return fail(MCPT_ERR_INVALID, "unknown variant");
     int rc = ensure_uploaded();
     if (rc) return rc;
     cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : c.stream;

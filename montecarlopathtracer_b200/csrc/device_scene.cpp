@@ -79,6 +79,8 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     for (size_t k = 0; k < out.leaf_ids.size(); ++k)
         for (int j = 0; j < 3; ++j) out.leaf_tris[3 * k + j] = out.tri_isect[3 * static_cast<size_t>(out.leaf_ids[k]) + j];
 
+    build_ropes(tree, out);
+
     // running CDF over emitter area for area-uniform light sampling
     double run = 0.0;
     for (size_t i = 0; i < areas.size(); ++i) {

@@ -18,6 +18,7 @@
 //   leaf_tris  3 x float4 per LEAF REFERENCE: the tri_isect record of leaf_ids[k] copied in place k, with the
 //                 triangle id in the free lane {e1.xyz, id bits}: a leaf's triangles are consecutive 48-byte
 //                 records and the render path needs no id -> record indirection (tuning build variant)
+//   rope_nodes, leaf_hdr   stackless traversal: see kd_ropes.cpp
 //   tri_shade  3 x float4 per triangle {n0.xyz, matId bits} {n1.xyz, 0} {n2.xyz, 0}
 //   mats       3 x float4 per material {Ka, Ns} {Kd, Tr} {Ks, Ni}
 //   emitters   3 x float4 per emitting triangle {a.xyz, area} {b-a, cdf} {c-a, triangle id bits}
@@ -37,6 +38,8 @@ struct DScene {
     const uint32_t* leaf_ids;
     const float4* tri_isect;
     const float4* leaf_tris;
+    const uint2* rope_nodes;
+    const float4* leaf_hdr;
     const float4* tri_shade;
     const float4* mats;
     const float4* emitters;
@@ -54,18 +57,19 @@ struct DCamera {
 
 struct PackedScene {
     std::vector<float4> ref_nodes;
-    std::vector<uint2> kd_nodes;
+    std::vector<uint2> kd_nodes, rope_nodes;
     std::vector<uint32_t> leaf_ids;
-    std::vector<float4> tri_isect, leaf_tris, tri_shade, mats, emitters;
+    std::vector<float4> tri_isect, leaf_tris, leaf_hdr, tri_shade, mats, emitters;
     float bmin[3], bmax[3];
     float emitter_area = 0.0f;
     size_t bytes() const {
-        return ref_nodes.size() * 16 + kd_nodes.size() * 8 + leaf_ids.size() * 4 +
-               (tri_isect.size() + leaf_tris.size() + tri_shade.size() + mats.size() + emitters.size()) * 16;
+        return ref_nodes.size() * 16 + (kd_nodes.size() + rope_nodes.size()) * 8 + leaf_ids.size() * 4 +
+               (tri_isect.size() + leaf_tris.size() + leaf_hdr.size() + tri_shade.size() + mats.size() + emitters.size()) * 16;
     }
 };
 
 void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out);
+void build_ropes(const HostTree& tree, PackedScene& out);  // kd_ropes.cpp; needs kd_nodes of pack_scene
 DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height);
 
 }  // namespace mcpt

@@ -10,7 +10,7 @@
 
 // Shipping configuration of the persistent-lane kernel (profiles/r1_tuning.md).
 #ifndef MCPT_SM_VARIANT
-#define MCPT_SM_VARIANT 5
+#define MCPT_SM_VARIANT 23
 #endif
 #ifndef MCPT_SM_MIN_BLOCKS
 #define MCPT_SM_MIN_BLOCKS 4
@@ -27,8 +27,9 @@ __global__ void __launch_bounds__(256) intersect_kernel(const DScene sc, const f
     if (i >= n) return;
     const float* r = rays + 6 * i;
     const float ox = __ldg(r), oy = __ldg(r + 1), oz = __ldg(r + 2), dx = __ldg(r + 3), dy = __ldg(r + 4), dz = __ldg(r + 5);
-    const Hit h = variant == MCPT_ISECT_KD ? intersect_kd(sc, ox, oy, oz, dx, dy, dz)
-                                           : intersect_ref(sc, ox, oy, oz, dx, dy, dz);
+    const Hit h = variant == MCPT_ISECT_ROPES ? intersect_ropes(sc, ox, oy, oz, dx, dy, dz)
+                  : variant == MCPT_ISECT_KD  ? intersect_kd(sc, ox, oy, oz, dx, dy, dz)
+                                              : intersect_ref(sc, ox, oy, oz, dx, dy, dz);
     tri[i] = static_cast<int32_t>(h.tri);
     if (t) t[i] = h.t;
     if (beta) beta[i] = h.beta;
@@ -43,7 +44,8 @@ __global__ void __launch_bounds__(256) tally_kernel(const DScene sc, const float
     TraversalTally tally;
     if (i < n) {
         const float* r = rays + 6 * i;
-        if (variant == MCPT_ISECT_KD) intersect_kd(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
+        if (variant == MCPT_ISECT_ROPES) intersect_ropes(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
+        else if (variant == MCPT_ISECT_KD) intersect_kd(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
         else intersect_ref(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
     }
     uint32_t a = tally.popped, b = tally.entered, c = tally.tris;
@@ -106,7 +108,7 @@ cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
-    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale;
+    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = 16;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
     render_kernel<RNG, KD, NEE, MOMENTS><<<grid, 256, 0, stream>>>(p);
@@ -118,20 +120,19 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
-    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale;
+    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = r.cam_threshold;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
 #ifdef MCPT_TUNE
     // tuning build: every kernel variant x residency for the headline combination (Philox, no NEE, no moments)
     if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
-#define MCPT_V(MB, V) render_kernel_sm<RNG, NEE, MOMENTS, MB, V><<<grid, 256, 0, stream>>>(p, r.shade_threshold); break;
-#define MCPT_MB(V) switch (r.min_blocks) { case 5: MCPT_V(5, V) case 3: MCPT_V(3, V) default: MCPT_V(4, V) } break;
-        if (r.variant & 8) { render_kernel_sm<RNG, NEE, MOMENTS, 4, 13><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
-        switch (r.variant & 7) {
-            case 0: MCPT_MB(0) case 1: MCPT_MB(1) case 2: MCPT_MB(2) case 3: MCPT_MB(3)
-            case 4: MCPT_MB(4) case 5: MCPT_MB(5) case 6: MCPT_MB(6) default: MCPT_MB(7)
+#define MCPT_V(V) case V: render_kernel_sm<RNG, NEE, MOMENTS, 4, V><<<grid, 256, 0, stream>>>(p, r.shade_threshold); break;
+        if (r.variant == 23 && r.min_blocks == 5) { render_kernel_sm<RNG, NEE, MOMENTS, 5, 23><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
+        if (r.variant == 23 && r.min_blocks == 3) { render_kernel_sm<RNG, NEE, MOMENTS, 3, 23><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
+        switch (r.variant) {
+            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20)
+            default: return cudaErrorInvalidValue;
         }
-#undef MCPT_MB
 #undef MCPT_V
         return cudaGetLastError();
     }

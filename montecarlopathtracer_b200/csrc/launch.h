@@ -25,6 +25,7 @@ struct RenderLaunch {
     int shade_threshold;   // lanes that must be waiting before the warp leaves the traverse phase
     int min_blocks;        // tuning builds only: 2, 3 or 4 resident 256-thread blocks per SM (register cap 128 / 85 / 64)
     int variant;           // tuning builds only: VAR bits of render_kernel_sm
+    int cam_threshold;     // camera-ray queue refill threshold (lanes)
 };
 
 // Number of kernels launched is returned through *launches (adds to it).

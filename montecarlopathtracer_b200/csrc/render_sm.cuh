@@ -22,11 +22,16 @@ enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 
 // VAR (tuning knobs, profiles/r1_tuning.md):
 //   bit 0  leaf triangles are read as consecutive records from leaf_tris (no id -> record indirection);
-//   bit 1  tri_test_flat: no early exits, one combined rejection in front of the divides (needs bit 0);
-//   bit 2  tri_test<true> (division-free rejections, intersect.cuh).
+//   bit 1  stackless traversal over neighbour links (kd_ropes.cpp): a ray starts in the leaf that contains its
+//          origin (hint: the leaf where the previous ray of the path ended) and walks leaf to leaf;
+//   bit 2  tri_test<true> (division-free rejections, intersect.cuh);
+//   bit 4  camera-ray queue: the next sample's primary ray is generated ahead of time, for many lanes at once,
+//          and parked in shared memory (in-place generation runs with ~2.6 of 32 lanes).
 template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR>
 __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
-    constexpr bool LEAFREC = (VAR & 1) != 0, FLATTRI = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0;
+    constexpr bool LEAFREC = (VAR & 1) != 0, ROPES = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0, CAMQ = (VAR & 16) != 0;
+    __shared__ float camq[CAMQ ? 7 * 256 : 1];  // CAMQ: parked primary ray {o, d, rng state} per thread
+    bool camReady = false;
     uint32_t st[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
     uint32_t px, py;
     thread_pixel(px, py);
@@ -46,6 +51,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
     uint32_t nearBits = 0;                                  // bit a: d[a] < 0 -> the right child is nearer
     float tmin = 0, tmax = 0, best = 10000.0f, hbeta = 0, hgamma = 0;
     uint32_t htri = 0xFFFFFFFFu, node = 0, li = 0, lend = 0;
+    uint32_t leaf = 0, hintLeaf = 0xFFFFFFFFu, camLeaf = 0xFFFFFFFFu;              // ROPES: current leaf; leaf where the path's last hit was found
     int top = 0;
     uint2 stack[MCPT_KD_STACK];
     F3 thr = f3(1, 1, 1), cur = f3(0, 0, 0), acc = f3(0, 0, 0), acc2 = f3(0, 0, 0);
@@ -56,7 +62,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
 
     // Prepares traversal of the ray (ox..dz): reciprocal, child order bits, clip against the root box.
     auto begin_ray = [&]() {
-        ix = __fdiv_rn(1.0f, dx); iy = __fdiv_rn(1.0f, dy); iz = __fdiv_rn(1.0f, dz);
+        ix = __frcp_rn(dx); iy = __frcp_rn(dy); iz = __frcp_rn(dz);  // correctly rounded 1/d, same bits as 1.0f / d
         nearBits = (ix < 0.0f ? 1u : 0u) | (iy < 0.0f ? 2u : 0u) | (iz < 0.0f ? 4u : 0u);
         tmin = 0.0f; tmax = 10000.0f;
         float tn = (p.sc.bmin[0] - ox) * ix, tf = (p.sc.bmax[0] - ox) * ix;
@@ -73,6 +79,28 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
         node = 0; top = 0;
         ++nrays;
         state = (tmin <= tmax) ? ST_INNER : ST_SHADE;  // a ray that misses the scene box is shaded as a miss
+        if (ROPES && state == ST_INNER) {
+            // tmin doubles as the distance already covered.  The walk starts in the leaf that contains the
+            // entry point q: the hinted leaf when q lies in its cell (a bounce ray starts where the previous
+            // ray ended; a camera ray enters where this pixel's previous sample entered), else located from
+            // the root.
+            const bool cam = bounce == 0u && !shadow;
+            const uint32_t hint = cam ? camLeaf : hintLeaf;
+            float qx = ox, qy = oy, qz = oz;
+            if (tmin > 0.0f) {
+                qx = fminf(fmaxf(ox + tmin * dx, p.sc.bmin[0]), p.sc.bmax[0]);
+                qy = fminf(fmaxf(oy + tmin * dy, p.sc.bmin[1]), p.sc.bmax[1]);
+                qz = fminf(fmaxf(oz + tmin * dz, p.sc.bmin[2]), p.sc.bmax[2]);
+            }
+            bool located = false;
+            if (hint != 0xFFFFFFFFu) {
+                const float4 h0 = ldg4(p.sc.leaf_hdr + 4 * hint), h1 = ldg4(p.sc.leaf_hdr + 4 * hint + 1);
+                located = qx >= h0.x && qx <= h1.x && qy >= h0.y && qy <= h1.y && qz >= h0.z && qz <= h1.z;
+            }
+            if (STATS) { st[3] += 1; st[4] += located ? 1u : 0u; }
+            leaf = located ? hint : rope_locate(p.sc, 0u, qx, qy, qz, nearBits);
+            if (cam) camLeaf = leaf;
+        }
     };
     auto start_sample = [&]() {
         rng.start(pixel, p.seed, static_cast<uint32_t>(p.sample_begin + s), p.frame_seeds ? p.frame_seeds[s] : 0u);
@@ -83,6 +111,31 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
         ox = o.x; oy = o.y; oz = o.z; dx = d.x; dy = d.y; dz = d.z;
         thr = f3(1, 1, 1); cur = f3(0, 0, 0);
         bounce = 0; lastWasNee = false; shadow = false;
+    };
+    // CAMQ: generate sample s+1's primary ray for every lane that has none parked, once enough lanes need one.
+    auto refill_camera_queue = [&]() {
+        const bool need = !camReady && inside && state != ST_DEAD && s + 1 < sEnd;
+        if (__popc(__ballot_sync(0xFFFFFFFFu, need)) < p.cam_threshold) return;
+        if (need) {
+            RNG r;
+            r.start(pixel, p.seed, static_cast<uint32_t>(p.sample_begin + s + 1), p.frame_seeds ? p.frame_seeds[s + 1] : 0u);
+            float u1 = 0.5f, u2 = 0.5f;
+            if (p.jitter) { u1 = r.next(); u2 = r.next(); }
+            F3 o, d;
+            camera_ray(p.cam, p.width, p.height, px, py, u1, u2, o, d);
+            float* q = camq + threadIdx.x;
+            q[0] = o.x; q[256] = o.y; q[512] = o.z; q[768] = d.x; q[1024] = d.y; q[1280] = d.z;
+            q[1536] = __uint_as_float(r.save());
+            camReady = true;
+        }
+    };
+    auto take_parked_sample = [&]() {
+        const float* q = camq + threadIdx.x;
+        ox = q[0]; oy = q[256]; oz = q[512]; dx = q[768]; dy = q[1024]; dz = q[1280];
+        rng.resume(pixel, p.seed, static_cast<uint32_t>(p.sample_begin + s), __float_as_uint(q[1536]));
+        thr = f3(1, 1, 1); cur = f3(0, 0, 0);
+        bounce = 0; lastWasNee = false; shadow = false;
+        camReady = false;
     };
     // After a leaf: stop if the closest hit lies before the end of this cell, else continue with the
     // next cell along the ray (cells are contiguous: its tmin is this cell's tmax).
@@ -128,12 +181,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
         for (; li < lend; ++li) {
             float t, be, ga;
             if (STATS) ++myTris;
-            if (LEAFREC && FLATTRI) {
-                uint32_t id;
-                if (tri_test_flat(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, id)) {
-                    best = t; htri = id; hbeta = be; hgamma = ga;
-                }
-            } else if (LEAFREC) {
+            if (LEAFREC || ROPES) {
                 uint32_t id;
                 if (tri_test<FASTREJ>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, &id)) {
                     best = t; htri = id; hbeta = be; hgamma = ga;
@@ -154,6 +202,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
     while (true) {
         {
             // ================= SHADE: consume the hit, produce the next ray ====================
+            if (CAMQ) refill_camera_queue();
             if (STATS) { st[7] += 1; st[8] += __popc(__ballot_sync(0xFFFFFFFFu, state == ST_SHADE)); }
             if (state == ST_SHADE) {
                 bool done = false, haveRay = false;
@@ -165,6 +214,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                 } else if (htri == 0xFFFFFFFFu) {
                     done = true;  // rtx.hlsl:370
                 } else {
+                    if (ROPES) hintLeaf = leaf;  // the walk stopped in the cell that contains the hit point
                     rng.set_slot(bounce + 1u);
                     if (bounce >= p.depth * 3u) {
                         done = true;  // :313-316
@@ -246,7 +296,12 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                     acc = acc + cur;
                     if (MOMENTS) acc2 = acc2 + cur * cur;
                     ++s;
-                    if (s < sEnd) { start_sample(); haveRay = true; } else state = ST_DEAD;
+                    if (s < sEnd) {
+                        if (CAMQ && camReady) take_parked_sample(); else start_sample();
+                        haveRay = true;
+                    } else {
+                        state = ST_DEAD;
+                    }
                 }
                 if (haveRay) begin_ray();
             }
@@ -255,7 +310,24 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
         // ================= TRAVERSE: one leaf visit per round, until enough lanes wait ==========
         while (true) {
             if (STATS) { myNodes = 0; myTris = 0; st[1] += 1; st[2] += __popc(__ballot_sync(0xFFFFFFFFu, state == ST_INNER)); }
-            if (state == ST_INNER) {
+            if (ROPES) {
+                if (state == ST_INNER) {
+                    const float4 h0 = ldg4(p.sc.leaf_hdr + 4 * leaf), h1 = ldg4(p.sc.leaf_hdr + 4 * leaf + 1);
+                    li = __float_as_uint(h0.w); lend = li + __float_as_uint(h1.w);
+                    test_leaf();
+                    const LeafExit e = leaf_exit(p.sc, leaf, h0, h1, ox, oy, oz, ix, iy, iz, nearBits);
+                    if (best <= e.t || e.rope == 0xFFFFFFFFu) {
+                        state = ST_SHADE;
+                    } else {
+                        tmin = fmaxf(tmin, e.t);
+                        float qx = ox + tmin * dx, qy = oy + tmin * dy, qz = oz + tmin * dz;
+                        if (e.axis == 0u) qx = e.plane;
+                        if (e.axis == 1u) qy = e.plane;
+                        if (e.axis == 2u) qz = e.plane;
+                        leaf = rope_locate(p.sc, e.rope, qx, qy, qz, nearBits);
+                    }
+                }
+            } else if (state == ST_INNER) {
                 descend();
                 test_leaf();
                 pop_or_finish();
@@ -275,6 +347,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
     }
     if (STATS) {
         st[9] = __reduce_add_sync(0xFFFFFFFFu, st[9]);
+        if (ROPES) { st[3] = __reduce_add_sync(0xFFFFFFFFu, st[3]); st[4] = __reduce_add_sync(0xFFFFFFFFu, st[4]); }
         if ((threadIdx.x & 31u) == 0u)
             for (int k = 1; k < 10; ++k) atomicAdd(p.ray_counter + k, static_cast<unsigned long long>(st[k]));
     }

@@ -45,6 +45,9 @@ struct RngPhilox {
         k0 = pixel; k1 = seed; sample = sampleIndex; slot = 0; draw = 0;
     }
     __device__ __forceinline__ void set_slot(uint32_t s) { slot = s; draw = 0; }
+    // A stream parked after the camera draws and picked up later (counter-based: nothing to carry).
+    __device__ __forceinline__ uint32_t save() const { return 0u; }
+    __device__ __forceinline__ void resume(uint32_t pixel, uint32_t seed, uint32_t sampleIndex, uint32_t) { start(pixel, seed, sampleIndex, 0u); }
     __device__ __forceinline__ float next() {
         if ((draw & 3u) == 0u) {
             uint32_t o[4];
@@ -75,6 +78,8 @@ struct RngReference {
         next();
     }
     __device__ __forceinline__ void set_slot(uint32_t) {}
+    __device__ __forceinline__ uint32_t save() const { return sd; }
+    __device__ __forceinline__ void resume(uint32_t, uint32_t, uint32_t, uint32_t saved) { sd = saved; }
     __device__ __forceinline__ float next() {
         sd = 16807u * (sd % 127773u) - 2836u * (sd / 127773u);
         if (sd > 0x7FFFFFFFu) sd += 0x7FFFFFFFu;

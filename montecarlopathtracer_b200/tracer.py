@@ -22,7 +22,7 @@ BUILD_REFERENCE, BUILD_SAH = 0, 1
 LOADER_TINYOBJ, LOADER_OBJREADER = 0, 1
 RNG_PHILOX, RNG_REFERENCE = 0, 1
 FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL, FLAG_SIMPLE_KERNEL = 1, 2, 4, 8, 16
-ISECT_REFERENCE, ISECT_KD = 0, 1
+ISECT_REFERENCE, ISECT_KD, ISECT_ROPES = 0, 1, 2
 ERR_NO_DEVICE = 4
 
 _vp = C.c_void_p

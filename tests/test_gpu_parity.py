@@ -71,8 +71,9 @@ def _brute_force(oracle, s, rays):
     return oracle.scene(s, one).intersect(rays)
 
 
+@pytest.mark.parametrize("variant", [1, 2], ids=["kd_stack", "ropes"])
 @pytest.mark.parametrize("name", ["scene01", "scene02", "scene03"])
-def test_intersection_kd_traversal_equals_reference(gpu, oracle, scenes, name):
+def test_intersection_kd_traversal_equals_reference(gpu, oracle, scenes, name, variant):
     """The render path's front-to-back plane traversal returns the same closest hit (same id, same bits).
     The only permitted differences are rays where the REFERENCE's clipped-box slab test drops a real hit
     through rounding (SURVEY 7.3 "AABB-cull semantics"): there the KD traversal must return the exact
@@ -83,7 +84,7 @@ def test_intersection_kd_traversal_equals_reference(gpu, oracle, scenes, name):
     cam = oracle.cfg(512, 512, 1, 5, jitter=0, eye=SCENE_CAMERA[name], at=(0, 5, SCENE_CAMERA[name][2] - 1))
     for rays in (oracle.primary_rays(cam), _random_rays(s, 1 << 18, seed=2)):
         tri, t, b, g, _ = osc.intersect(rays)
-        ktri, kt, kb, kg = T.intersect_batch(rays, T.ISECT_KD)
+        ktri, kt, kb, kg = T.intersect_batch(rays, variant)
         bad = np.flatnonzero((tri != ktri) | ((tri >= 0) & (_bits(t) != _bits(kt))))
         assert len(bad) <= 1e-4 * len(rays), f"{len(bad)} of {len(rays)} rays differ, first {bad[:5]}"
         if len(bad):
@@ -106,7 +107,7 @@ def test_intersection_edge_cases(gpu, oracle, scenes):
             rays.append(o + d)
     rays = np.array(rays, np.float32)
     tri, t, b, g, _ = osc.intersect(rays)
-    for variant in (T.ISECT_REFERENCE, T.ISECT_KD):
+    for variant in (T.ISECT_REFERENCE, T.ISECT_KD, T.ISECT_ROPES):
         gtri, gt, gb, gg = T.intersect_batch(rays, variant)
         assert np.array_equal(tri, gtri), variant
         assert np.array_equal(_bits(t)[tri >= 0], _bits(gt)[tri >= 0])
@@ -240,15 +241,16 @@ def test_render_ragged_sizes(gpu, oracle, scenes):
         assert close.mean() >= min(0.95, 1 - 1.5 / (W * H)), (W, H, close.mean())
 
 
+@pytest.mark.parametrize("variant", [1, 2], ids=["kd_stack", "ropes"])
 @pytest.mark.parametrize("name", ["scene01", "scene02", "scene03"])
-def test_sah_build_mode_gives_same_hits(gpu, oracle, scenes, name):
+def test_sah_build_mode_gives_same_hits(gpu, oracle, scenes, name, variant):
     """The library's own SAH tree (perfect splits) must find the same closest hits, bit for bit, as
     the reference tree; any difference must again be a hit the reference's box test dropped."""
     T, s = gpu, scenes[name]
     _load(T, s, T.BUILD_SAH)
     rays = _random_rays(s, 1 << 18, seed=3)
     tri, t, _, _, _ = oracle.scene(s).intersect(rays)
-    gtri, gt, _, _ = T.intersect_batch(rays, T.ISECT_KD)
+    gtri, gt, _, _ = T.intersect_batch(rays, variant)
     bad = np.flatnonzero((gtri != tri) | ((tri >= 0) & (_bits(gt) != _bits(t))))
     assert len(bad) <= 1e-4 * len(rays), len(bad)
     if len(bad):
