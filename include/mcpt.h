@@ -53,6 +53,15 @@ enum {
     MCPT_RNG_REFERENCE = 1  /* rtx.hlsl:61-82 TEA+LCG with the mt19937(1234) frame seeds (GraphicsRTX.cpp:170-171) */
 };
 
+/* Which of the reference's two estimators / cameras a render follows (never mixed). */
+enum {
+    MCPT_TRACER_MCRT = 0,      /* rtx.hlsl: +-0.5 px jitter, fovy, origin on the image plane, roulette from max_depth,
+                                  kill at 3*max_depth, untinted glass -- the KD-tree path, canonical            */
+    MCPT_TRACER_CUDA_TWIN = 1  /* CUTracer.cu:98-218: +-1 px jitter, `fovy` is the HORIZONTAL fov (60 deg) with square
+                                  pixels, origin at the eye, max_depth (7) scattering events + one final gather, no
+                                  roulette, glass tinted by Kd, Ns truncated to unsigned                        */
+};
+
 enum {
     MCPT_FLAG_NEE = 1u,        /* next-event estimation to the emitters at Lambert vertices   */
     MCPT_FLAG_MOMENTS = 2u,    /* also accumulate per-pixel sum of squares                    */
@@ -93,6 +102,7 @@ typedef struct mcpt_render_cfg {
     float eye[3], at[3], up[3]; /* D3DXMatrixLookAtRH arguments (GraphicsRTX.cpp:175-178)       */
     float fovy;              /* radians (GraphicsRTX.cpp:183)                                   */
     float emission_scale;    /* 1 for the KD-tree tracer; the CUDA twin multiplies Ka by ILLUM  */
+    int32_t tracer_mode;     /* MCPT_TRACER_*                                                   */
 } mcpt_render_cfg;
 
 typedef struct mcpt_counters {
@@ -135,6 +145,9 @@ int mcpt_destroy_geometry(void);
 
 /* ---- PW::Tracer::RenderScene (CUTracer.cu:340-404) / Graphics::OnUpdate x spp -------------- */
 void mcpt_default_render_cfg(mcpt_render_cfg* cfg, int width, int height, int spp, int max_depth);
+/* RenderScene(sceneID, ...) of the CUDA tracer as a cfg: CUDA_TWIN mode, depth 7, hfov 60 deg, ILLUM = 10,
+ * eye (0,5,17) for scene 1 and (0,5,23) otherwise (CUTracer.cu:347-374, stdafx.h:41-45). */
+void mcpt_cuda_twin_render_cfg(mcpt_render_cfg* cfg, int width, int height, int spp, int scene_id);
 /* host_rgb: width*height*3 floats, row-major, top row first, LINEAR MEAN radiance (same layout as
  * `hostcolor`). host_m2 (optional): mean of squared samples per channel (needs MCPT_FLAG_MOMENTS). */
 int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m2);

@@ -37,6 +37,8 @@ int check_cfg(const mcpt_render_cfg* cfg) {
     if (cfg->sample_offset < 0) return fail(MCPT_ERR_INVALID, "negative sample_offset");
     if (cfg->rng_mode != MCPT_RNG_PHILOX && cfg->rng_mode != MCPT_RNG_REFERENCE) return fail(MCPT_ERR_INVALID, "unknown rng_mode");
     if (!(cfg->fovy > 0.0f && cfg->fovy < 3.14159f)) return fail(MCPT_ERR_INVALID, "fovy out of range");
+    if (cfg->tracer_mode != MCPT_TRACER_MCRT && cfg->tracer_mode != MCPT_TRACER_CUDA_TWIN) return fail(MCPT_ERR_INVALID, "unknown tracer_mode");
+    if (cfg->tracer_mode == MCPT_TRACER_CUDA_TWIN && cfg->rng_mode == MCPT_RNG_REFERENCE) return fail(MCPT_ERR_INVALID, "the CUDA twin has no reproducible reference stream (cuRAND seeded from random_device, CUTracer.cu:375-376): use MCPT_RNG_PHILOX");
     return MCPT_OK;
 }
 
@@ -60,10 +62,17 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
 
     RenderLaunch r;
     r.sc = c.dscene;
-    r.cam = make_camera(cfg->eye, cfg->at, cfg->up, cfg->fovy, cfg->width, cfg->height);
+    const bool twin = cfg->tracer_mode == MCPT_TRACER_CUDA_TWIN;
+    r.cam = make_camera(cfg->eye, cfg->at, cfg->up, cfg->fovy, cfg->width, cfg->height, twin ? 1 : 0);
     r.width = cfg->width; r.height = cfg->height;
     r.sample_begin = cfg->sample_offset; r.sample_count = cfg->spp; r.chunks = chunks;
-    r.depth = static_cast<uint32_t>(cfg->max_depth); r.seed = cfg->seed;
+    // rtx.hlsl:313-328: roulette from `depth`, kill at 3*depth.  CUTracer.cu:103-176: `depth` scattering events,
+    // then one gather, no roulette.
+    r.depth = twin ? 0xFFFFFFFFu : static_cast<uint32_t>(cfg->max_depth);
+    r.kill_at = twin ? 0xFFFFFFFFu : 3u * static_cast<uint32_t>(cfg->max_depth);
+    r.gather_at = twin ? static_cast<uint32_t>(cfg->max_depth) : 0xFFFFFFFFu;
+    r.twin = twin ? 1u : 0u;
+    r.seed = cfg->seed;
     r.jitter = (cfg->flags & MCPT_FLAG_NO_JITTER) ? 0u : 1u;
     r.emission_scale = cfg->emission_scale;
     r.slices = c.d_slices.ptr;
@@ -157,6 +166,16 @@ void mcpt_default_render_cfg(mcpt_render_cfg* cfg, int width, int height, int sp
     cfg->up[0] = 0; cfg->up[1] = 1; cfg->up[2] = 0;
     cfg->fovy = 3.141592654f / 4.0f;  // float(D3DX_PI) / 4, GraphicsRTX.cpp:183
     cfg->emission_scale = 1.0f;
+}
+
+void mcpt_cuda_twin_render_cfg(mcpt_render_cfg* cfg, int width, int height, int spp, int scene_id) {
+    if (!cfg) return;
+    mcpt_default_render_cfg(cfg, width, height, spp, 7);                 // depth literal, CUTracer.cu:212
+    cfg->tracer_mode = MCPT_TRACER_CUDA_TWIN;
+    cfg->eye[2] = scene_id == 1 ? 17.0f : 23.0f;                        // CUTracer.cu:349,363
+    cfg->at[2] = cfg->eye[2] - 1.0f;
+    cfg->fovy = 60.0f * 3.14159265359f / 180.0f;                         // projFOV = 60, PW_PI (stdafx.h:46)
+    cfg->emission_scale = 10.0f;                                         // ILLUM (stdafx.h:45)
 }
 
 int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m2) {
@@ -256,7 +275,7 @@ int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays) 
         gen.discard(static_cast<unsigned long long>(sample));
         frameSeed = static_cast<uint32_t>(gen());
     }
-    DCamera cam = make_camera(cfg->eye, cfg->at, cfg->up, cfg->fovy, cfg->width, cfg->height);
+    DCamera cam = make_camera(cfg->eye, cfg->at, cfg->up, cfg->fovy, cfg->width, cfg->height, cfg->tracer_mode == MCPT_TRACER_CUDA_TWIN ? 1 : 0);
     c.counters.launches = 0;
     if ((e = launch_primary_rays(cam, cfg->width, cfg->height, sample, cfg->seed, (cfg->flags & MCPT_FLAG_NO_JITTER) ? 0u : 1u,
                                  cfg->rng_mode, frameSeed, c.d_rays.ptr, c.stream, &c.counters.launches)) != cudaSuccess)

@@ -5,7 +5,7 @@
 //
 //   mcpt_cli --scene FILE.obj|FILE.mcpt [--loader tinyobj|objreader] [--tree sah|reference]
 //            [--w W --h H --spp N --depth D] [--eye x,y,z --at x,y,z --fovy DEG] [--emission S]
-//            [--seed K --rng philox|reference] [--nee] [--step N] [--out out.png] [--pfm out.pfm] [--device I]
+//            [--twin SCENEID (before --eye/--depth overrides)] [--seed K --rng philox|reference] [--nee] [--step N] [--out out.png] [--pfm out.pfm] [--device I]
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -49,6 +49,10 @@ int main(int argc, char** argv) {
         else if (a == "--seed") cfg.seed = static_cast<uint32_t>(std::strtoul(val(), nullptr, 10));
         else if (a == "--rng") cfg.rng_mode = std::string(val()) == "reference" ? MCPT_RNG_REFERENCE : MCPT_RNG_PHILOX;
         else if (a == "--nee") cfg.flags |= MCPT_FLAG_NEE;
+        else if (a == "--twin") {  // the CUDA tracer's estimator and camera (RenderScene(sceneID, ...))
+            const int w = cfg.width, h = cfg.height, n = cfg.spp;
+            mcpt_cuda_twin_render_cfg(&cfg, w, h, n, std::atoi(val()));
+        }
         else if (a == "--step") step = std::atoi(val());
         else if (a == "--out") out = val();
         else if (a == "--pfm") pfm = val();

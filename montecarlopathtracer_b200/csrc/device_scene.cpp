@@ -102,7 +102,7 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
 // D3DXMatrixLookAtRH / Inverse / PerspectiveFovRH in closed form (GraphicsRTX.cpp:173-184):
 // zaxis = normalize(eye - at), xaxis = normalize(up x zaxis), yaxis = zaxis x xaxis,
 // inverse view rows = xaxis, yaxis, zaxis, eye; _22 = cot(fovy/2), _11 = _22 / (w/h).
-DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height) {
+DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height, int twin) {
     DCamera cam;
     auto norm = [](float v[3]) {
         float l = sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
@@ -117,6 +117,8 @@ DCamera make_camera(const float eye[3], const float at[3], const float up[3], fl
     float aspect = 1.0f * width / height;
     cam.p22 = static_cast<float>(1.0 / std::tan(static_cast<double>(fovy) * 0.5));
     cam.p11 = cam.p22 / aspect;
+    cam.tan_half = tanf(fovy * 0.5f);  // tan(projFOV * PW_PI / 360), CUTracer.cu:202
+    cam.twin = twin;
     return cam;
 }
 

@@ -53,6 +53,8 @@ struct DScene {
 struct DCamera {
     float inv[4][3];
     float p11, p22;
+    float tan_half;  // CUDA-twin camera: tan(hfov / 2)
+    int twin;        // 0: rtx.hlsl camera, 1: CUTracer.cu:189-212
 };
 
 struct PackedScene {
@@ -70,6 +72,6 @@ struct PackedScene {
 
 void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out);
 void build_ropes(const HostTree& tree, PackedScene& out);  // kd_ropes.cpp; needs kd_nodes of pack_scene
-DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height);
+DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height, int twin = 0);
 
 }  // namespace mcpt

@@ -108,7 +108,7 @@ cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
-    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = 16;
+    p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = 16;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
     render_kernel<RNG, KD, NEE, MOMENTS><<<grid, 256, 0, stream>>>(p);
@@ -120,7 +120,7 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
-    p.depth = r.depth; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = r.cam_threshold;
+    p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = r.cam_threshold;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
 #ifdef MCPT_TUNE

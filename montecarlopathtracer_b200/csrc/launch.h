@@ -13,7 +13,7 @@ struct RenderLaunch {
     DCamera cam;
     int width, height;
     int sample_begin, sample_count, chunks;
-    uint32_t depth, seed, jitter;
+    uint32_t depth, kill_at, gather_at, twin, seed, jitter;
     float emission_scale;
     float4* slices;        // [chunks][h][w] scratch (or the destination itself when chunks == 1 and !accumulate)
     float4* slices_sq;     // nullptr unless moments

@@ -19,7 +19,10 @@ struct RenderParams {
     int sample_begin;      // absolute index of the first sample of this launch
     int sample_count;      // samples per pixel in this launch
     int chunks;            // sample range is split over gridDim.z chunks, one output slice each
-    uint32_t depth;        // the shader's `depth`
+    uint32_t depth;        // roulette from this bounce on (the shader's `depth`, rtx.hlsl:317); 0xFFFFFFFF = never
+    uint32_t kill_at;      // a hit at this bounce index returns 0 (3 * depth, rtx.hlsl:313)
+    uint32_t gather_at;    // CUDA twin: at this bounce index only emission is gathered, no scattering (CUTracer.cu:162-175)
+    uint32_t twin;         // CUDA twin shading rules: glass tinted by Kd, Ns truncated to unsigned
     uint32_t seed;
     uint32_t jitter;
     int cam_threshold;     // render_kernel_sm, camera-ray queue: lanes that must need a refill before the warp refills
@@ -33,6 +36,22 @@ struct RenderParams {
 // rtx.hlsl:384-398
 __device__ __forceinline__ void camera_ray(const DCamera& cam, int width, int height, uint32_t px, uint32_t py,
                                            float u1, float u2, F3& org, F3& dir) {
+    if (cam.twin) {
+        // CUTracer.cu:195-212: +-1 px, horizontal fov, the 2.0 / 1.0 literals make this double arithmetic
+        const float bx = static_cast<float>(px) + (u1 * 2.0f - 1.0f);
+        const float by = static_cast<float>(py) + (u2 * 2.0f - 1.0f);
+        const float t0 = static_cast<float>((2.0 * bx / width - 1) * cam.tan_half);
+        const float t1 = static_cast<float>((1.0 * height / width - 2.0 * by / width) * cam.tan_half);
+        F3 w;
+        w.x = cam.inv[0][0] * t0 + cam.inv[1][0] * t1 - cam.inv[2][0];
+        w.y = cam.inv[0][1] * t0 + cam.inv[1][1] * t1 - cam.inv[2][1];
+        w.z = cam.inv[0][2] * t0 + cam.inv[1][2] * t1 - cam.inv[2][2];
+        const float len = sqrtf(w.x * w.x + w.y * w.y + w.z * w.z);
+        if (fabsf(len) > MCPT_EPS) { w.x /= len; w.y /= len; w.z /= len; }  // Utils.hpp:27-34
+        dir = w;
+        org = f3(cam.inv[3][0], cam.inv[3][1], cam.inv[3][2]);
+        return;
+    }
     const float biasx = static_cast<float>(px) + (u1 - 0.5f);
     const float biasy = static_cast<float>(py) + (u2 - 0.5f);
     const float d0 = (2.0f * biasx / static_cast<float>(width) - 1) / cam.p11;
@@ -108,7 +127,7 @@ __global__ void __launch_bounds__(256) render_kernel(const RenderParams p) {
             done = true;  // rtx.hlsl:370
         } else {
             rng.set_slot(bounce + 1u);
-            if (bounce >= p.depth * 3u) {
+            if (bounce >= p.kill_at) {
                 done = true;  // :313-316
             } else if (bounce >= p.depth) {
                 const float illum = fmaxf(fmaxf(thr.x, thr.y), thr.z);  // :317-328
@@ -122,6 +141,8 @@ __global__ void __launch_bounds__(256) render_kernel(const RenderParams p) {
                     // :329-334; with NEE the light was already gathered at the previous Lambert vertex
                     if (!(NEE && lastWasNee)) cur = cur + thr * f3(mKa.x, mKa.y, mKa.z) * p.emission_scale;
                     done = true;
+                } else if (bounce >= p.gather_at) {
+                    done = true;  // CUDA twin: the last intersect only gathers emission (CUTracer.cu:162-175)
                 } else {
                     const float4 s1 = ldg4(p.sc.tri_shade + 3 * h.tri + 1), s2 = ldg4(p.sc.tri_shade + 3 * h.tri + 2);
                     const float4 mKd = ldg4(p.sc.mats + 3 * mat + 1);
@@ -133,15 +154,16 @@ __global__ void __launch_bounds__(256) render_kernel(const RenderParams p) {
                     if (mKd.w > 0) {  // Tr > 0, :342-346
                         const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);
                         dir = sample_fresnel(rng, normal, dir, mKd.w, mKs.w);
+                        if (p.twin) thr = thr * f3(mKd.x, mKd.y, mKd.z);  // CUTracer.cu:131-133
                     } else if (mKa.w > 1) {  // Ns > 1, :348-352
                         const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);
-                        dir = sample_phong(rng, normal, dir, mKa.w);
+                        dir = sample_phong(rng, normal, dir, p.twin ? static_cast<float>(static_cast<uint32_t>(mKa.w)) : mKa.w);  // Utils.hpp:72
                         thr = thr * f3(mKs.x, mKs.y, mKs.z);
                     } else {  // :354-365
                         const bool flip = dot(dir, normal) > 0;
                         dir = flip ? -sample_hemi(rng, normal) : sample_hemi(rng, normal);
                         thr = thr * f3(mKd.x, mKd.y, mKd.z);
-                        if (NEE && p.sc.num_emitters > 0 && bounce + 1u < p.depth * 3u) {
+                        if (NEE && p.sc.num_emitters > 0 && bounce + 1u < p.kill_at) {
                             // Next-event estimation of what the reference would collect at bounce+1:
                             // thr*Kd * Ka * (cos_x / pi) * |cos_y| * A / r^2, visible iff the first hit from
                             // hp + 0.01 w is the sampled emitter triangle.

@@ -216,7 +216,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                 } else {
                     if (ROPES) hintLeaf = leaf;  // the walk stopped in the cell that contains the hit point
                     rng.set_slot(bounce + 1u);
-                    if (bounce >= p.depth * 3u) {
+                    if (bounce >= p.kill_at) {
                         done = true;  // :313-316
                     } else if (bounce >= p.depth) {
                         const float illum = fmaxf(fmaxf(thr.x, thr.y), thr.z);  // :317-328
@@ -229,6 +229,8 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                         if (mKa.x > 0 || mKa.y > 0 || mKa.z > 0) {  // :329-334
                             if (!(NEE && lastWasNee)) cur = cur + thr * f3(mKa.x, mKa.y, mKa.z) * p.emission_scale;
                             done = true;
+                        } else if (bounce >= p.gather_at) {
+                            done = true;  // CUDA twin: the last intersect only gathers emission (CUTracer.cu:162-175)
                         } else {
                             const float4 s1 = ldg4(p.sc.tri_shade + 3 * htri + 1), s2 = ldg4(p.sc.tri_shade + 3 * htri + 2);
                             const float4 mKd = ldg4(p.sc.mats + 3 * mat + 1);
@@ -241,15 +243,16 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                             if (mKd.w > 0) {  // Tr > 0, :342-346
                                 const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);
                                 dir = sample_fresnel(rng, normal, dir, mKd.w, mKs.w);
+                                if (p.twin) thr = thr * f3(mKd.x, mKd.y, mKd.z);  // CUTracer.cu:131-133
                             } else if (mKa.w > 1) {  // Ns > 1, :348-352
                                 const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);
-                                dir = sample_phong(rng, normal, dir, mKa.w);
+                                dir = sample_phong(rng, normal, dir, p.twin ? static_cast<float>(static_cast<uint32_t>(mKa.w)) : mKa.w);  // Utils.hpp:72
                                 thr = thr * f3(mKs.x, mKs.y, mKs.z);
                             } else {  // :354-365
                                 const bool flip = dot(dir, normal) > 0;
                                 dir = flip ? -sample_hemi(rng, normal) : sample_hemi(rng, normal);
                                 thr = thr * f3(mKd.x, mKd.y, mKd.z);
-                                if (NEE && p.sc.num_emitters > 0 && bounce + 1u < p.depth * 3u) {
+                                if (NEE && p.sc.num_emitters > 0 && bounce + 1u < p.kill_at) {
                                     // what the reference would collect at bounce+1, gathered by area sampling
                                     // of the emitters (DESIGN.md "next-event estimation")
                                     rng.set_slot(0x80000000u | (bounce + 1u));

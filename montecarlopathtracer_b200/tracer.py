@@ -23,6 +23,7 @@ LOADER_TINYOBJ, LOADER_OBJREADER = 0, 1
 RNG_PHILOX, RNG_REFERENCE = 0, 1
 FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL, FLAG_SIMPLE_KERNEL = 1, 2, 4, 8, 16
 ISECT_REFERENCE, ISECT_KD, ISECT_ROPES = 0, 1, 2
+TRACER_MCRT, TRACER_CUDA_TWIN = 0, 1
 ERR_NO_DEVICE = 4
 
 _vp = C.c_void_p
@@ -44,7 +45,7 @@ class RenderCfg(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("max_depth", C.c_int32),
                 ("sample_offset", C.c_int32), ("seed", C.c_uint32), ("rng_mode", C.c_int32), ("flags", C.c_uint32),
                 ("eye", C.c_float * 3), ("at", C.c_float * 3), ("up", C.c_float * 3), ("fovy", C.c_float),
-                ("emission_scale", C.c_float)]
+                ("emission_scale", C.c_float), ("tracer_mode", C.c_int32)]
 
 
 class Counters(C.Structure):
@@ -79,6 +80,8 @@ def lib() -> C.CDLL:
     L.mcpt_get_scene.argtypes = [_vp] * 5
     L.mcpt_default_render_cfg.argtypes = [C.POINTER(RenderCfg), C.c_int, C.c_int, C.c_int, C.c_int]
     L.mcpt_default_render_cfg.restype = None
+    L.mcpt_cuda_twin_render_cfg.argtypes = [C.POINTER(RenderCfg), C.c_int, C.c_int, C.c_int, C.c_int]
+    L.mcpt_cuda_twin_render_cfg.restype = None
     L.mcpt_render_scene.argtypes = [C.POINTER(RenderCfg), _vp, _vp]
     L.mcpt_render_accumulate_device.argtypes = [C.POINTER(RenderCfg), _vp, _vp, _vp]
     L.mcpt_intersect_batch.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp]
@@ -186,6 +189,18 @@ def get_scene():
 def render_cfg(width: int, height: int, spp: int, max_depth: int, **kw) -> RenderCfg:
     cfg = RenderCfg()
     lib().mcpt_default_render_cfg(C.byref(cfg), width, height, spp, max_depth)
+    for k, v in kw.items():
+        if k in ("eye", "at", "up"):
+            getattr(cfg, k)[:] = list(v)
+        else:
+            setattr(cfg, k, v)
+    return cfg
+
+
+def cuda_twin_render_cfg(width: int, height: int, spp: int, scene_id: int = 1, **kw) -> RenderCfg:
+    """The cfg of PW::Tracer::RenderScene(sceneID, ...) (CUTracer.cu:340-404)."""
+    cfg = RenderCfg()
+    lib().mcpt_cuda_twin_render_cfg(C.byref(cfg), width, height, spp, scene_id)
     for k, v in kw.items():
         if k in ("eye", "at", "up"):
             getattr(cfg, k)[:] = list(v)

@@ -32,6 +32,11 @@ typedef struct oracle_cfg {
     float fovy;             /* radians; GraphicsRTX.cpp:183 uses float(D3DX_PI)/4                */
     int32_t x0, y0, x1, y1; /* pixel window [x0,x1) x [y0,y1) actually rendered (bounded CPU samples) */
     int32_t threads;        /* OpenMP threads, 0 = all                                           */
+    int32_t tracer_mode;    /* 0: MCRT rtx.hlsl (KD path, canonical); 1: the CUDA twin's estimator and camera
+                               (CUTracer.cu:98-218): +-1 px jitter, fovy = HORIZONTAL fov, origin at the eye,
+                               `depth` scattering events + one final gather, no roulette, Kd-tinted glass,
+                               Ns truncated to unsigned, emission x emission_scale (ILLUM)                 */
+    float emission_scale;   /* 1 for rtx.hlsl; ILLUM = 10 for the twin (stdafx.h:45)                     */
 } oracle_cfg;
 
 typedef struct oracle_counters {

@@ -52,6 +52,22 @@ Camera make_camera(const oracle_cfg& cfg) {
 // rtx.hlsl:384-398.  u1,u2 are the two jitter draws (0.5 each when jitter is off).
 void camera_ray(const oracle_cfg& cfg, const Camera& cam, uint32_t px, uint32_t py, float u1, float u2,
                 V3& from, V3& dir) {
+    if (cfg.tracer_mode == 1) {
+        // CUTracer.cu:195-212: +-1 px jitter, horizontal fov, square pixels, the 2.0 / 1.0 literals make the
+        // arithmetic double; origin = camPos.  cam.inv rows are right, up, -forward, eye.
+        float biasx = px + (u1 * 2.0f - 1.0f);
+        float biasy = py + (u2 * 2.0f - 1.0f);
+        const float tanH = tanf(cfg.fovy * 0.5f);
+        float d[3] = {static_cast<float>((2.0 * biasx / cfg.width - 1) * tanH),
+                      static_cast<float>((1.0 * cfg.height / cfg.width - 2.0 * biasy / cfg.width) * tanH), -1.0f};
+        V3 w;
+        w.x = cam.inv[0][0] * d[0] + cam.inv[1][0] * d[1] + cam.inv[2][0] * d[2];
+        w.y = cam.inv[0][1] * d[0] + cam.inv[1][1] * d[1] + cam.inv[2][1] * d[2];
+        w.z = cam.inv[0][2] * d[0] + cam.inv[1][2] * d[1] + cam.inv[2][2] * d[2];
+        dir = normalize_twin(w);
+        from = {cam.inv[3][0], cam.inv[3][1], cam.inv[3][2]};
+        return;
+    }
     float biasx = px + (u1 - 0.5f);
     float biasy = py + (u2 - 0.5f);
     float d[3] = {(2.0f * biasx / cfg.width - 1) / cam.p11, (1 - 2.0f * biasy / cfg.height) / cam.p22, -1.0f};
@@ -116,6 +132,8 @@ void oracle_default_cfg(oracle_cfg* cfg, int width, int height, int spp, int dep
     cfg->fovy = 3.141592654f / 4.0f;  // static_cast<FLOAT>(D3DX_PI) / 4.0f
     cfg->x0 = cfg->y0 = cfg->x1 = cfg->y1 = 0;
     cfg->threads = 0;
+    cfg->tracer_mode = 0;
+    cfg->emission_scale = 1.0f;
 }
 
 void* oracle_scene_create(const float* verts, int nV, const float* normals, int nN, const uint32_t* tris,
@@ -257,7 +275,9 @@ void oracle_render(void* scene, const oracle_cfg* cfgp, double* sum, double* sum
                 start_sample(cfg, static_cast<uint32_t>(y) * cfg.width + x, frame, seeds[f], rng, u1, u2);
                 V3 from, dir;
                 camera_ray(cfg, cam, x, y, u1, u2, from, dir);
-                V3 c = sample_mc(s, rng, from, dir, static_cast<uint32_t>(cfg.depth), tally);
+                V3 c = cfg.tracer_mode == 1 ? sample_mc_twin(s, rng, from, dir, static_cast<uint32_t>(cfg.depth), cfg.emission_scale, tally)
+                                            : sample_mc(s, rng, from, dir, static_cast<uint32_t>(cfg.depth), tally);
+                if (cfg.tracer_mode == 0 && cfg.emission_scale != 1.0f) { c.x *= cfg.emission_scale; c.y *= cfg.emission_scale; c.z *= cfg.emission_scale; }
                 acc[0] += c.x; acc[1] += c.y; acc[2] += c.z;
                 acc2[0] += static_cast<double>(c.x) * c.x; acc2[1] += static_cast<double>(c.y) * c.y;
                 acc2[2] += static_cast<double>(c.z) * c.z;

@@ -79,5 +79,7 @@ V3 sample_hemi(Rng& rng, V3 normal);
 V3 sample_phong(Rng& rng, V3 normal, V3 dir, float Ns);
 V3 sample_fresnel(Rng& rng, V3 normal, V3 dir, float Tr, float Ni);
 V3 sample_mc(const Scene& scene, Rng& rng, V3 from, V3 dir, uint32_t depth, Tally& tally);
+V3 sample_mc_twin(const Scene& scene, Rng& rng, V3 from, V3 dir, uint32_t maxDepth, float illum, Tally& tally);
+V3 normalize_twin(V3 v);
 
 }  // namespace oracle

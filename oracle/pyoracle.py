@@ -57,7 +57,7 @@ class Cfg(C.Structure):
                 ("rng_mode", C.c_int32), ("seed", C.c_uint32), ("sample_offset", C.c_int32),
                 ("jitter", C.c_int32), ("eye", C.c_float * 3), ("at", C.c_float * 3), ("up", C.c_float * 3),
                 ("fovy", C.c_float), ("x0", C.c_int32), ("y0", C.c_int32), ("x1", C.c_int32),
-                ("y1", C.c_int32), ("threads", C.c_int32)]
+                ("y1", C.c_int32), ("threads", C.c_int32), ("tracer_mode", C.c_int32), ("emission_scale", C.c_float)]
 
 
 class Counters(C.Structure):

@@ -284,4 +284,52 @@ V3 sample_mc(const Scene& scene, Rng& rng, V3 from, V3 dir, uint32_t depth, Tall
     return {0, 0, 0};
 }
 
+// ---- the CUDA twin (CVMCTracer/CVMCTracer/CUDA) ---------------------------------------------------------
+// CUDA/Utils.hpp:27-34: divide by the length unless it is (almost) zero.
+V3 normalize_twin(V3 v) {
+    float len = sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
+    if (fabsf(len) > CS_FLT_EPSILON) {
+        v.x /= len; v.y /= len; v.z /= len;
+    }
+    return v;
+}
+
+// CUTracer.cu:98-177 over the same scene tables (the twin binds one material per OBJ group; the loader
+// already gives every triangle its group's material, CUTracer.cu:300-308).  Same samplers as rtx.hlsl
+// (Utils.hpp:46-137 is the same math) except that samplePhong takes Ns as an unsigned (Utils.hpp:72).
+V3 sample_mc_twin(const Scene& scene, Rng& rng, V3 from, V3 dir, uint32_t maxDepth, float illum, Tally& tally) {
+    V3 color = {1, 1, 1};
+    for (uint32_t depth = 0; depth < maxDepth; ++depth) {
+        Hit hit = intersect(scene, from, dir, tally);
+        if (hit.triID == 0xFFFFFFFFu) return {0, 0, 0};
+        rng.set_slot(depth + 1);
+        const Tri& tri = scene.tris[hit.triID];
+        const Material& m = scene.mats[tri.mat];
+        if (m.Ka[0] > 0 || m.Ka[1] > 0 || m.Ka[2] > 0) {
+            color.x *= m.Ka[0] * illum; color.y *= m.Ka[1] * illum; color.z *= m.Ka[2] * illum;
+            return color;
+        }
+        V3 normal = load3(scene.normals, tri.n[0]) * (1.0f - hit.beta - hit.gamma) + load3(scene.normals, tri.n[1]) * hit.beta +
+                    load3(scene.normals, tri.n[2]) * hit.gamma;
+        normal = normalize_twin(normal);
+        if (m.Tr > 0) {
+            dir = sample_fresnel(rng, normal, dir, m.Tr, m.Ni);
+            color = color * V3{m.Kd[0], m.Kd[1], m.Kd[2]};  // :131-133, the tint rtx.hlsl:345 comments out
+        } else if (m.Ns > 1) {
+            dir = sample_phong(rng, normal, dir, static_cast<float>(static_cast<uint32_t>(m.Ns)));
+            color = color * V3{m.Ks[0], m.Ks[1], m.Ks[2]};
+        } else {
+            color = color * V3{m.Kd[0], m.Kd[1], m.Kd[2]};
+            dir = dot(dir, normal) > 0 ? -sample_hemi(rng, normal) : sample_hemi(rng, normal);
+        }
+        from = hit.p + dir * 0.01f;
+    }
+    // :162-175 the final gather: whatever is hit contributes throughput * Ka * ILLUM (zero for non-emitters)
+    Hit hit = intersect(scene, from, dir, tally);
+    if (hit.triID == 0xFFFFFFFFu) return {0, 0, 0};
+    const Material& m = scene.mats[scene.tris[hit.triID].mat];
+    color.x *= m.Ka[0] * illum; color.y *= m.Ka[1] * illum; color.z *= m.Ka[2] * illum;
+    return color;
+}
+
 }  // namespace oracle

@@ -294,3 +294,48 @@ def test_tessellated_surface_scene(gpu, oracle, scenes):
             assert np.array_equal(btri, ktri[bad]) and np.array_equal(_bits(bt), _bits(kt[bad]))
         mean = T.render_scene(T.render_cfg(W, H, spp, 8, seed=6))
         assert np.isclose(mean, osum / spp, rtol=1e-3, atol=1e-5).all(-1).mean() > 0.97
+
+
+TWIN_FOVY = np.float32(60) * np.float32(3.14159265359) / np.float32(180)
+
+
+@pytest.mark.parametrize("jitter", [0, 1])
+def test_cuda_twin_primary_rays_bit_equal(gpu, oracle, scenes, jitter):
+    """CUTracer.cu:189-212: +-1 px jitter, hfov 60 deg in double arithmetic, origin at the eye."""
+    T = gpu
+    _load(T, scenes["scene01"])
+    for scene_id, z in ((1, 17.0), (2, 23.0)):
+        gcfg = T.cuda_twin_render_cfg(100, 75, 1, scene_id, seed=5, flags=0 if jitter else T.FLAG_NO_JITTER)
+        assert gcfg.max_depth == 7 and gcfg.emission_scale == 10.0 and gcfg.eye[2] == z
+        ocfg = oracle.cfg(100, 75, 1, 7, tracer_mode=1, rng_mode=1, seed=5, jitter=jitter, eye=(0, 5, z), at=(0, 5, z - 1), fovy=TWIN_FOVY)
+        assert np.float32(gcfg.fovy) == TWIN_FOVY
+        for sample in (0, 2):
+            assert np.array_equal(_bits(T.primary_rays(gcfg, sample)), _bits(oracle.primary_rays(ocfg, sample)))
+
+
+@pytest.mark.parametrize("name,scene_id", [("scene01", 1), ("scene02", 2), ("scene01_lambert", 1)])
+@pytest.mark.parametrize("simple", [0, 1])
+def test_cuda_twin_render_same_paths_as_oracle(gpu, oracle, scenes, name, scene_id, simple):
+    """The CUDA twin's estimator (7 scattering events + one gather, no roulette, Ka * ILLUM, Kd-tinted glass) on the
+    shared Philox stream: GPU and oracle trace the same paths."""
+    T, s = gpu, scenes[name]
+    _load(T, s, T.BUILD_SAH)
+    W, H, spp = 96, 72, 8
+    z = 17.0 if scene_id == 1 else 23.0
+    gcfg = T.cuda_twin_render_cfg(W, H, spp, scene_id, seed=4, flags=T.FLAG_SIMPLE_KERNEL if simple else 0)
+    ocfg = oracle.cfg(W, H, spp, 7, tracer_mode=1, emission_scale=10.0, rng_mode=1, seed=4, eye=(0, 5, z), at=(0, 5, z - 1), fovy=TWIN_FOVY)
+    osum, osq, _, ocnt = oracle.scene(s).render(ocfg)
+    mean, m2 = T.render_scene(gcfg, moments=True)
+    c = T.counters()
+    assert c.paths == ocnt.paths and abs(int(c.rays) - int(ocnt.rays)) <= 0.002 * ocnt.rays
+    assert c.rays <= 8 * c.paths
+    close = np.isclose(mean, osum / spp, rtol=1e-3, atol=1e-4).all(-1)
+    assert close.mean() > 0.97, close.mean()
+    assert mean.max() <= 10.0 * s.mats[:, :3].max() + 1e-4 and mean.max() > 1.0     # Ka x ILLUM, throughput <= 1
+
+
+def test_cuda_twin_rejects_reference_stream(gpu, scenes):
+    T = gpu
+    _load(T, scenes["scene01"])
+    with pytest.raises(T.McptError, match="no reproducible reference stream"):
+        T.render_scene(T.cuda_twin_render_cfg(16, 16, 1, 1, rng_mode=T.RNG_REFERENCE))

@@ -191,3 +191,24 @@ def test_triangle_test_equals_the_cuda_twins_arithmetic_with_reference_det(oracl
             assert (ot[0].view(np.uint32), ob[0].view(np.uint32), og[0].view(np.uint32)) == (t.view(np.uint32), beta.view(np.uint32), gamma.view(np.uint32))
             checked += 1
     assert checked > 50
+
+
+def test_cuda_twin_mode_semantics(oracle, scenes):
+    """CUTracer.cu:98-218 restated: origin at the eye, horizontal fov 60 deg with square pixels, at most
+    depth + 1 = 8 intersect calls per path, no roulette (throughput <= 1, so radiance <= Ka * ILLUM)."""
+    cfg = oracle.cfg(80, 60, 1, 7, tracer_mode=1, emission_scale=10.0, jitter=0, fovy=np.float32(60 * np.float32(3.14159265359) / 180))
+    rays = oracle.primary_rays(cfg).reshape(60, 80, 6)
+    assert np.array_equal(rays[..., :3], np.broadcast_to(np.float32([0, 5, 17]), (60, 80, 3)))
+    assert np.allclose(np.linalg.norm(rays[..., 3:], axis=-1), 1, atol=1e-6)
+    # jitter off: u = 0.5 -> bias = pixel index exactly; column 0 looks along -tan(30 deg), column w/2 straight ahead
+    d = rays[30, :, 3:]
+    assert np.allclose(d[0, 0] / -d[0, 2], -np.tan(np.pi / 6), atol=1e-6) and abs(d[40, 0]) < 1e-7
+    assert abs(rays[30, 40, 4]) < 1e-7 and np.allclose(rays[0, 40, 4] / -rays[0, 40, 5], 0.75 * np.tan(np.pi / 6), atol=1e-6)
+    sc = oracle.scene(scenes["scene01"])
+    cfg = oracle.cfg(40, 30, 8, 7, tracer_mode=1, emission_scale=10.0, rng_mode=1, seed=2, fovy=np.float32(60 * np.float32(3.14159265359) / 180))
+    s, _, _, c = sc.render(cfg)
+    assert s.max() / 8 <= 8.0 + 1e-5 and s.max() > 0
+    assert c.paths == 40 * 30 * 8 and c.paths <= c.rays <= 8 * c.paths
+    # the MCRT estimator on the same scene may take up to 3 * depth + 1 rays and applies roulette: a different sample set
+    s2, _, _, c2 = sc.render(oracle.cfg(40, 30, 8, 7, rng_mode=1, seed=2))
+    assert c2.rays != c.rays
