@@ -4,6 +4,7 @@
 #include "device_scene.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace mcpt {
@@ -15,6 +16,39 @@ inline uint32_t as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u;
 
 void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) {
     const size_t nN = tree.num_nodes(), nT = scene.num_triangles(), nM = scene.num_materials();
+    // Device order of the leaves: depth first (left subtree first), so that the id lists, triangle records and
+    // headers of spatially neighbouring leaves are neighbours in memory (the host tree keeps the reference's
+    // breadth-first leaf order).  Matters once the scene outgrows L1/L2 (K4: L2 hit rate, DRAM page locality).
+    out.leaf_order.assign(nN, 0xFFFFFFFFu);
+    std::vector<uint32_t> devOffset(nN, 0u);
+    out.leaf_ids.clear();
+    out.leaf_ids.reserve(tree.leaf_ids.size() + 1);
+    {
+        std::vector<uint32_t> todo(1, 0u);
+        uint32_t ordinal = 0;
+        const char* bfs = std::getenv("MCPT_LEAF_BFS");  // A/B knob: keep the breadth-first leaf order
+        if (bfs && *bfs == '1') {
+            todo.clear();
+            for (uint32_t k = 0; k < nN; ++k)
+                if (tree.split_axis[k] == 0) {
+                    out.leaf_order[k] = ordinal++;
+                    devOffset[k] = static_cast<uint32_t>(out.leaf_ids.size());
+                    for (uint32_t i = 0; i < tree.leaf_count[k]; ++i) out.leaf_ids.push_back(tree.leaf_ids[tree.leaf_offset[k] + i]);
+                }
+        }
+        while (!todo.empty()) {
+            const uint32_t k = todo.back();
+            todo.pop_back();
+            if (tree.split_axis[k] != 0) {
+                todo.push_back(tree.left[k] + 1u);
+                todo.push_back(tree.left[k]);
+            } else {
+                out.leaf_order[k] = ordinal++;
+                devOffset[k] = static_cast<uint32_t>(out.leaf_ids.size());
+                for (uint32_t i = 0; i < tree.leaf_count[k]; ++i) out.leaf_ids.push_back(tree.leaf_ids[tree.leaf_offset[k] + i]);
+            }
+        }
+    }
     out.ref_nodes.resize(2 * nN);
     out.kd_nodes.resize(nN);
     for (size_t k = 0; k < nN; ++k) {
@@ -26,16 +60,15 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
             kx = as_uint(tree.split_value[k]);
             ky = (tree.left[k] << 2) | (tree.split_axis[k] - 1u);
         } else {
-            a = tree.leaf_offset[k];
+            a = devOffset[k];
             b = 0x80000000u | tree.leaf_count[k];
-            kx = tree.leaf_offset[k];
+            kx = devOffset[k];
             ky = (tree.leaf_count[k] << 2) | 3u;
         }
         out.ref_nodes[2 * k] = make_float4(bb[0], bb[1], bb[2], as_float(a));
         out.ref_nodes[2 * k + 1] = make_float4(bb[3], bb[4], bb[5], as_float(b));
         out.kd_nodes[k] = make_uint2(kx, ky);
     }
-    out.leaf_ids = tree.leaf_ids;
     if (out.leaf_ids.empty()) out.leaf_ids.push_back(0u);
     for (int i = 0; i < 3; ++i) { out.bmin[i] = tree.aabb[i]; out.bmax[i] = tree.aabb[3 + i]; }
 

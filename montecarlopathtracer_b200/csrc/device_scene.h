@@ -61,6 +61,7 @@ struct PackedScene {
     std::vector<float4> ref_nodes;
     std::vector<uint2> kd_nodes, rope_nodes;
     std::vector<uint32_t> leaf_ids;
+    std::vector<uint32_t> leaf_order;  // per node: depth-first ordinal of a leaf (host only)
     std::vector<float4> tri_isect, leaf_tris, leaf_hdr, tri_shade, mats, emitters;
     float bmin[3], bmax[3];
     float emitter_area = 0.0f;

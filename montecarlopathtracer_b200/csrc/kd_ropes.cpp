@@ -51,7 +51,7 @@ struct Builder {
     void walk(uint32_t node, const Cell& cell, const uint32_t ropes[6]) {
         if (t.split_axis[node] == 0) {
             const uint32_t k = leafOrdinal[node];
-            out.leaf_hdr[4 * k] = make_float4(cell.lo[0], cell.lo[1], cell.lo[2], as_float(t.leaf_offset[node]));
+            out.leaf_hdr[4 * k] = make_float4(cell.lo[0], cell.lo[1], cell.lo[2], as_float(out.kd_nodes[node].x));
             out.leaf_hdr[4 * k + 1] = make_float4(cell.hi[0], cell.hi[1], cell.hi[2], as_float(t.leaf_count[node]));
             out.leaf_hdr[4 * k + 2] = make_float4(as_float(ropes[0]), as_float(ropes[1]), as_float(ropes[2]), as_float(ropes[3]));
             out.leaf_hdr[4 * k + 3] = make_float4(as_float(ropes[4]), as_float(ropes[5]), 0.0f, 0.0f);
@@ -85,8 +85,8 @@ void build_ropes(const HostTree& tree, PackedScene& out) {
     out.rope_nodes = out.kd_nodes;
     for (size_t k = 0; k < nN; ++k)
         if (tree.split_axis[k] == 0) {
-            b.leafOrdinal[k] = leaves;
-            out.rope_nodes[k].x = leaves;
+            b.leafOrdinal[k] = out.leaf_order[k];  // depth-first ordinal (pack_scene)
+            out.rope_nodes[k].x = out.leaf_order[k];
             ++leaves;
         }
     out.leaf_hdr.assign(4 * static_cast<size_t>(leaves), make_float4(0, 0, 0, 0));
