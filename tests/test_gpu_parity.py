@@ -339,3 +339,28 @@ def test_cuda_twin_rejects_reference_stream(gpu, scenes):
     _load(T, scenes["scene01"])
     with pytest.raises(T.McptError, match="no reproducible reference stream"):
         T.render_scene(T.cuda_twin_render_cfg(16, 16, 1, 1, rng_mode=T.RNG_REFERENCE))
+
+
+def test_headless_cli_renders_a_scene_file(gpu, scenes, tmp_path):
+    """mcpt_cli: scene -> progressive render -> PNG + PFM + one JSON line (the reference's main.cpp sequence, headless)."""
+    import json, subprocess
+    from conftest import ROOT
+    import os
+    cli = os.path.join(ROOT, "montecarlopathtracer_b200", "lib", "mcpt_cli")
+    out, pfm = str(tmp_path / "o.png"), str(tmp_path / "o.pfm")
+    r = subprocess.run([cli, "--scene", os.path.join(ROOT, "scenes", "scene01.mcpt"), "--w", "64", "--h", "48", "--spp", "6", "--step", "2",
+                        "--depth", "5", "--seed", "3", "--out", out, "--pfm", pfm], capture_output=True, text=True, cwd=str(tmp_path), timeout=120)
+    assert r.returncode == 0, r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["paths"] == 64 * 48 * 6 and line["rays"] >= line["paths"]
+    assert open(out, "rb").read(8) == b"\x89PNG\r\n\x1a\n"
+    assert sorted(f for f in os.listdir(tmp_path) if f.startswith("step")) == ["step000000.png", "step000001.png", "step000002.png"]
+    data = open(pfm, "rb").read()
+    img = np.frombuffer(data[len(b"PF\n64 48\n-1.0\n"):], np.float32).reshape(48, 64, 3)[::-1]
+    # the three 2-sample steps compose to the single 6-sample render of the library
+    T = gpu
+    T.load_scene_file(os.path.join(ROOT, "scenes", "scene01.mcpt"), T.BUILD_SAH)
+    want = T.render_scene(T.render_cfg(64, 48, 6, 5, seed=3))
+    assert np.allclose(img, want, atol=2e-6)
+    r = subprocess.run([cli, "--scene", str(tmp_path / "missing.obj")], capture_output=True, text=True)
+    assert r.returncode != 0 and "load scene" in r.stderr
