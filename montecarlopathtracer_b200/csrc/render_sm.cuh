@@ -319,6 +319,11 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                     li = __float_as_uint(h0.w); lend = li + __float_as_uint(h1.w);
                     test_leaf();
                     const LeafExit e = leaf_exit(p.sc, leaf, h0, h1, ox, oy, oz, ix, iy, iz, nearBits);
+                    // No hop counter here (it costs a register the kernel does not have; intersect_ropes keeps one):
+                    // the walk terminates structurally.  The face taken on each axis is fixed by the ray's sign bits,
+                    // a rope's subtree lies wholly beyond that face, so the cell's bound on the exit axis moves
+                    // strictly in the sign direction every hop whatever the float values (NaN included) and the
+                    // number of hops is bounded by the number of split planes.
                     if (best <= e.t || e.rope == 0xFFFFFFFFu) {
                         state = ST_SHADE;
                     } else {
