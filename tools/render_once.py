@@ -1,0 +1,11 @@
+"""One 1024x1024x64spp render of a scene file through the C ABI (for ncu captures of kernel variants)."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from montecarlopathtracer_b200 import tracer as T
+T.initialize(0)
+T.load_scene_file(os.path.join(ROOT, "scenes", sys.argv[1] if len(sys.argv) > 1 else "scene01_lambert.mcpt"), 1)
+cfg = T.render_cfg(1024, 1024, int(sys.argv[2]) if len(sys.argv) > 2 else 64, 8, eye=(0, 5, 17.0), at=(0, 5, 16.0))
+T.render_scene(cfg)
+c = T.counters()
+print("%7.1f Mp/s" % (c.paths / c.kernel_ms / 1e3))
