@@ -173,6 +173,11 @@ int mcpt_get_counters(mcpt_counters* out);
 /* Measured FP32 FMA issue rate of the bound device in GFLOP/s (roofline denominator for the
  * intersection / shading arithmetic; the reference publishes nothing comparable). */
 int mcpt_measure_fp32_peak(double* gflops);
+/* Self-check of the kernels' shared-reciprocal division (intersect.cuh: div3_rn) against the IEEE
+ * divide it stands for: n pseudo-random (n0, n1, n2, d) quadruples with exponents spread over
+ * 2^-spread .. 2^+spread, every quotient compared bit for bit.  *mismatches must come back 0;
+ * *fast_path = how many quadruples took the shared-reciprocal branch (so the check is not vacuous). */
+int mcpt_selfcheck_div3(int64_t n, uint32_t seed, int spread, uint64_t* mismatches, uint64_t* fast_path);
 /* ---- image output (CUTracer.cu:383-396 step PNGs, GraphicsRTX.cpp:223-226 temp.png) ---------- */
 /* rgb: width*height*3 linear floats, top row first.  PNG stores clamp(pow(v, 1/gamma)) in 8 bits
  * (gamma 2.2 = the display value of rtx.hlsl:402; 1.0 = the CUDA tracer's linear dump). */

@@ -14,20 +14,31 @@ using namespace mcpt;
 
 namespace {
 
-// Enough threads to fill 148 SMs several times over; beyond that one thread per pixel keeps all
-// of a pixel's samples in registers.
-int pick_chunks(int width, int height, int spp) {
-    const long long pixels = static_cast<long long>(width) * height;
-    const long long target = 148LL * 2048 * 2;
-    long long chunks = (target + pixels - 1) / pixels;
-    chunks = std::max(1LL, std::min<long long>(chunks, spp));
-    return static_cast<int>(std::min<long long>(chunks, 64));
-}
-
 int env_int(const char* name, int dflt) {
     const char* v = std::getenv(name);
     return v && *v ? std::atoi(v) : dflt;
 }
+
+// How many slices the spp of a pixel are cut into (grid.z; each slice accumulates into its own buffer, one
+// reduce pass adds them).  Two reasons to cut: (1) small images: enough threads to fill 148 SMs several times
+// over; (2) the tail: a block carries all the samples of its 16x16 tile, the 4 096 blocks of a 1024^2 image
+// are 6.9 waves of 148 x 4 resident blocks and the last wave ran the SMs 7 % below their average active time
+// (profiles/r1d_*: sm__cycles_active.avg against .max) -- aim at >= 24 waves while a slice keeps >= 64 spp
+// (block start-up and drain are per slice).  K2: 4 slices of 256 spp, +5 % (profiles/r1_tuning.md).
+int pick_chunks(int width, int height, int spp) {
+    const long long pixels = static_cast<long long>(width) * height;
+    const long long target = 148LL * 2048 * 2;
+    long long chunks = (target + pixels - 1) / pixels;
+    const long long tiles = ((width + 15LL) / 16) * ((height + 15LL) / 16);
+    const long long forTail = std::min<long long>((24LL * 148 * 4 + tiles - 1) / tiles, spp / 64);
+    chunks = std::max(chunks, forTail);
+    chunks = std::max(1LL, std::min<long long>(chunks, spp));
+    chunks = std::min<long long>(chunks, 64);
+    const int forced = env_int("MCPT_CHUNKS", 0);  // tuning knob
+    if (forced > 0) chunks = std::min(forced, spp);
+    return static_cast<int>(chunks);
+}
+
 
 int check_cfg(const mcpt_render_cfg* cfg) {
     if (!cfg) return fail(MCPT_ERR_INVALID, "null render cfg");
@@ -86,7 +97,7 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.state_machine = (cfg->flags & MCPT_FLAG_SIMPLE_KERNEL) == 0;
     r.shade_threshold = env_int("MCPT_SM_SHADE", 20);      // tuning knobs, defaults from profiles/r1_tuning.md
     r.min_blocks = env_int("MCPT_SM_MINBLOCKS", 4);
-    r.variant = env_int("MCPT_SM_VARIANT", 23);
+    r.variant = env_int("MCPT_SM_VARIANT", 55);
     r.cam_threshold = env_int("MCPT_SM_CAMR", 16);
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
         // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))
@@ -323,6 +334,22 @@ int mcpt_measure_fp32_peak(double* gflops) {
         if (rep > 0) best = std::max(best, static_cast<double>(blocks) * 256 * iters * 16 / (ms * 1e6));
     }
     *gflops = best;
+    return MCPT_OK;
+}
+
+int mcpt_selfcheck_div3(int64_t n, uint32_t seed, int spread, uint64_t* mismatches, uint64_t* fast_path) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!mismatches || !fast_path || n < 0 || spread < 0 || spread > 126) return fail(MCPT_ERR_INVALID, "bad self-check arguments");
+    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    cudaError_t e;
+    if ((e = c.d_counter.ensure(16)) != cudaSuccess) return fail_cuda(e, "alloc counters");
+    if ((e = cudaMemsetAsync(c.d_counter.ptr, 0, 16 * sizeof(unsigned long long), c.stream)) != cudaSuccess) return fail_cuda(e, "memset");
+    if ((e = launch_selfcheck_div3(n, seed, spread, c.d_counter.ptr, c.stream)) != cudaSuccess) return fail_cuda(e, "self-check");
+    unsigned long long h[2];
+    if ((e = cudaMemcpyAsync(h, c.d_counter.ptr, sizeof(h), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H");
+    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "self-check");
+    *mismatches = h[0]; *fast_path = h[1];
     return MCPT_OK;
 }
 

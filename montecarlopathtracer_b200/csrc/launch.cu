@@ -10,7 +10,7 @@
 
 // Shipping configuration of the persistent-lane kernel (profiles/r1_tuning.md).
 #ifndef MCPT_SM_VARIANT
-#define MCPT_SM_VARIANT 23
+#define MCPT_SM_VARIANT 55
 #endif
 #ifndef MCPT_SM_MIN_BLOCKS
 #define MCPT_SM_MIN_BLOCKS 4
@@ -103,6 +103,34 @@ __global__ void __launch_bounds__(256) fp32_peak_kernel(float* __restrict__ out,
     out[blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
 }
 
+// div3_rn against __fdiv_rn on pseudo-random operands (Philox), counters[0] = mismatching quotients,
+// counters[1] = quadruples that took the shared-reciprocal branch.
+__global__ void __launch_bounds__(256) selfcheck_div3_kernel(long long n, uint32_t seed, int spread, unsigned long long* counters) {
+    unsigned long long bad = 0, fast = 0;
+    for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += gridDim.x * 256ll) {
+        uint32_t o[4], e[4];
+        philox4x32_10(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32), 0u, 0u, seed, 0x51ED270Bu, o);
+        philox4x32_10(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32), 1u, 0u, seed, 0x51ED270Bu, e);
+        float v[4];
+        for (int k = 0; k < 4; ++k) {
+            // random sign and mantissa, exponent uniform in [-spread, spread]
+            const int ex = static_cast<int>(e[k] % static_cast<uint32_t>(2 * spread + 1)) - spread;
+            v[k] = __uint_as_float((o[k] & 0x807FFFFFu) | (static_cast<uint32_t>(127 + ex) << 23));
+        }
+        float a0, a1, a2;
+        div3_rn(v[0], v[1], v[2], v[3], a0, a1, a2);
+        const float b0 = __fdiv_rn(v[0], v[3]), b1 = __fdiv_rn(v[1], v[3]), b2 = __fdiv_rn(v[2], v[3]);
+        bad += (__float_as_uint(a0) != __float_as_uint(b0)) + (__float_as_uint(a1) != __float_as_uint(b1)) +
+               (__float_as_uint(a2) != __float_as_uint(b2));
+        const float ad = fabsf(v[3]);
+        const float nmin = fminf(fminf(fabsf(v[0]), fabsf(v[1])), fabsf(v[2])), nmax = fmaxf(fmaxf(fabsf(v[0]), fabsf(v[1])), fabsf(v[2]));
+        fast += (ad >= 0x1p-40f && ad <= 0x1p40f && nmin >= ad * 0x1p-40f && nmax <= ad * 0x1p40f) ? 1u : 0u;
+    }
+    bad = __reduce_add_sync(0xFFFFFFFFu, static_cast<unsigned>(bad));
+    fast = __reduce_add_sync(0xFFFFFFFFu, static_cast<unsigned>(fast));
+    if ((threadIdx.x & 31u) == 0u) { atomicAdd(counters, bad); atomicAdd(counters + 1, fast); }
+}
+
 template <class RNG, bool KD, bool NEE, bool MOMENTS>
 cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
@@ -130,7 +158,7 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
         if (r.variant == 23 && r.min_blocks == 5) { render_kernel_sm<RNG, NEE, MOMENTS, 5, 23><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
         if (r.variant == 23 && r.min_blocks == 3) { render_kernel_sm<RNG, NEE, MOMENTS, 3, 23><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
         switch (r.variant) {
-            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20)
+            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20) MCPT_V(55) MCPT_V(53)
             default: return cudaErrorInvalidValue;
         }
 #undef MCPT_V
@@ -196,6 +224,11 @@ cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int
 cudaError_t launch_tally(const DScene& sc, const float* rays, int64_t n, int variant, unsigned long long* out, cudaStream_t stream) {
     if (n <= 0) return cudaSuccess;
     tally_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(sc, rays, n, variant, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_selfcheck_div3(long long n, uint32_t seed, int spread, unsigned long long* counters, cudaStream_t stream) {
+    selfcheck_div3_kernel<<<148 * 8, 256, 0, stream>>>(n, seed, spread, counters);
     return cudaGetLastError();
 }
 

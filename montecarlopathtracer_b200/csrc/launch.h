@@ -48,5 +48,6 @@ cudaError_t launch_tally(const DScene& sc, const float* rays, int64_t n, int var
 
 // scratch: blocks*256 floats. flops = blocks*256*iters*16.
 cudaError_t launch_fp32_peak(float* scratch, int blocks, int iters, cudaStream_t stream);
+cudaError_t launch_selfcheck_div3(long long n, uint32_t seed, int spread, unsigned long long* counters, cudaStream_t stream);
 
 }  // namespace mcpt

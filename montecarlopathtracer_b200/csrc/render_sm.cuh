@@ -26,10 +26,12 @@ enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 //          origin (hint: the leaf where the previous ray of the path ended) and walks leaf to leaf;
 //   bit 2  tri_test<true> (division-free rejections, intersect.cuh);
 //   bit 4  camera-ray queue: the next sample's primary ray is generated ahead of time, for many lanes at once,
-//          and parked in shared memory (in-place generation runs with ~2.6 of 32 lanes).
+//          and parked in shared memory (in-place generation runs with ~2.6 of 32 lanes);
+//   bit 5  div3_rn: the three IEEE quotients of a surviving triangle share one reciprocal and one range guard.
 template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR>
 __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
-    constexpr bool LEAFREC = (VAR & 1) != 0, ROPES = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0, CAMQ = (VAR & 16) != 0;
+    constexpr bool LEAFREC = (VAR & 1) != 0, ROPES = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0, CAMQ = (VAR & 16) != 0,
+                   DIV3 = (VAR & 32) != 0;
     __shared__ float camq[CAMQ ? 7 * 256 : 1];  // CAMQ: parked primary ray {o, d, rng state} per thread
     bool camReady = false;
     uint32_t st[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
@@ -183,12 +185,12 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
             if (STATS) ++myTris;
             if (LEAFREC || ROPES) {
                 uint32_t id;
-                if (tri_test<FASTREJ>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, &id)) {
+                if (tri_test<FASTREJ, DIV3>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, &id)) {
                     best = t; htri = id; hbeta = be; hgamma = ga;
                 }
             } else {
                 const uint32_t id = __ldg(p.sc.leaf_ids + li);
-                if (tri_test<FASTREJ>(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
+                if (tri_test<FASTREJ, DIV3>(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
                     best = t; htri = id; hbeta = be; hgamma = ga;
                 }
             }

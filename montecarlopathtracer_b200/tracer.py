@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
     L.mcpt_get_counters.argtypes = [C.POINTER(Counters)]
     L.mcpt_traversal_stats.argtypes = [_vp, C.c_int64, C.c_int, _vp]
     L.mcpt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
+    L.mcpt_selfcheck_div3.argtypes = [C.c_int64, C.c_uint32, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.mcpt_write_png.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int, C.c_float]
     L.mcpt_write_pfm.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
     L.mcpt_last_error.restype = C.c_char_p
@@ -270,6 +271,14 @@ def measure_fp32_peak() -> float:
     g = C.c_double()
     _check(lib().mcpt_measure_fp32_peak(C.byref(g)))
     return g.value
+
+
+def selfcheck_div3(n: int, seed: int = 1, spread: int = 30) -> tuple:
+    """div3_rn (the kernels' shared-reciprocal division) against __fdiv_rn on n random quadruples with exponents
+    in 2^-spread..2^spread -> (mismatching quotients, quadruples that took the shared-reciprocal branch)."""
+    bad, fast = C.c_uint64(), C.c_uint64()
+    _check(lib().mcpt_selfcheck_div3(n, seed, spread, C.byref(bad), C.byref(fast)))
+    return bad.value, fast.value
 
 
 def write_png(path: str, rgb: np.ndarray, gamma: float = 2.2) -> None:

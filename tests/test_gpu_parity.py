@@ -115,6 +115,20 @@ def test_intersection_edge_cases(gpu, oracle, scenes):
     assert len(e[0]) == 0
 
 
+@pytest.mark.parametrize("spread,fast_expected", [(12, True), (45, True), (126, False)])
+def test_shared_reciprocal_division_is_ieee_division(gpu, spread, fast_expected):
+    """div3_rn (one reciprocal + one range guard for the three quotients of a triangle test) must give the bits of
+    the IEEE divide the reference's `/` is (rtx.hlsl:176-186), on 2^26 random quadruples per exponent spread:
+    inside the guarded range only, across its border, and over the whole float range."""
+    n = 1 << 26
+    bad, fast = gpu.selfcheck_div3(n, seed=20 + spread, spread=spread)
+    assert bad == 0
+    if fast_expected:
+        assert fast > n // 8      # the shared-reciprocal branch was really exercised
+    if spread <= 12:
+        assert fast == n          # |quotient| <= 2^24, |d| <= 2^12: every quadruple is inside the guard
+
+
 def _gate(gpu_mean, gpu_m2, o_sum, o_sq, spp, block=1):
     """mean relative error < 1 % and no pixel beyond 4 sigma, sigma^2 = (var_o + var_g)/spp.
     block > 1 applies the same test to block x block pixel means (variance of a block mean = mean
