@@ -218,6 +218,7 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                 } else {
                     if (ROPES) hintLeaf = leaf;  // the walk stopped in the cell that contains the hit point
                     rng.set_slot(bounce + 1u);
+                    rng.fill();  // once for the warp: roulette and every BSDF sampler below draw from this block
                     if (bounce >= p.kill_at) {
                         done = true;  // :313-316
                     } else if (bounce >= p.depth) {
@@ -252,7 +253,8 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                                 thr = thr * f3(mKs.x, mKs.y, mKs.z);
                             } else {  // :354-365
                                 const bool flip = dot(dir, normal) > 0;
-                                dir = flip ? -sample_hemi(rng, normal) : sample_hemi(rng, normal);
+                                const F3 lobe = sample_hemi(rng, normal);  // one copy for both signs
+                                dir = flip ? -lobe : lobe;
                                 thr = thr * f3(mKd.x, mKd.y, mKd.z);
                                 if (NEE && p.sc.num_emitters > 0 && bounce + 1u < p.kill_at) {
                                     // what the reference would collect at bounce+1, gathered by area sampling

@@ -41,22 +41,28 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
 struct RngPhilox {
     uint32_t k0, k1, sample, slot, draw;
     uint32_t b0, b1, b2, b3;
+    bool need;  // the block that holds draw `draw` has not been generated yet
     __device__ __forceinline__ void start(uint32_t pixel, uint32_t seed, uint32_t sampleIndex, uint32_t /*frameSeed*/) {
-        k0 = pixel; k1 = seed; sample = sampleIndex; slot = 0; draw = 0;
+        k0 = pixel; k1 = seed; sample = sampleIndex; slot = 0; draw = 0; need = true;
     }
-    __device__ __forceinline__ void set_slot(uint32_t s) { slot = s; draw = 0; }
+    __device__ __forceinline__ void set_slot(uint32_t s) { slot = s; draw = 0; need = true; }
+    // Generates the current block now.  Same numbers as leaving it to the first next(); a caller uses it to run the
+    // ten rounds once, with the whole warp, in front of code whose branches would each run their own copy.
+    __device__ __forceinline__ void fill() {
+        uint32_t o[4];
+        philox4x32_10(sample, slot, draw >> 2, 0u, k0, k1, o);
+        b0 = o[0]; b1 = o[1]; b2 = o[2]; b3 = o[3];
+        need = false;
+    }
     // A stream parked after the camera draws and picked up later (counter-based: nothing to carry).
     __device__ __forceinline__ uint32_t save() const { return 0u; }
     __device__ __forceinline__ void resume(uint32_t pixel, uint32_t seed, uint32_t sampleIndex, uint32_t) { start(pixel, seed, sampleIndex, 0u); }
     __device__ __forceinline__ float next() {
-        if ((draw & 3u) == 0u) {
-            uint32_t o[4];
-            philox4x32_10(sample, slot, draw >> 2, 0u, k0, k1, o);
-            b0 = o[0]; b1 = o[1]; b2 = o[2]; b3 = o[3];
-        }
+        if (need) fill();
         const uint32_t i = draw & 3u;
         const uint32_t x = i == 0 ? b0 : (i == 1 ? b1 : (i == 2 ? b2 : b3));
         ++draw;
+        need = (draw & 3u) == 0u;
         return static_cast<float>((x >> 8) + 1u) * (1.0f / 16777216.0f);
     }
 };
@@ -78,6 +84,7 @@ struct RngReference {
         next();
     }
     __device__ __forceinline__ void set_slot(uint32_t) {}
+    __device__ __forceinline__ void fill() {}
     __device__ __forceinline__ uint32_t save() const { return sd; }
     __device__ __forceinline__ void resume(uint32_t, uint32_t, uint32_t, uint32_t saved) { sd = saved; }
     __device__ __forceinline__ float next() {
