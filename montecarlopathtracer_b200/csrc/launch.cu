@@ -122,9 +122,7 @@ __global__ void __launch_bounds__(256) selfcheck_div3_kernel(long long n, uint32
         const float b0 = __fdiv_rn(v[0], v[3]), b1 = __fdiv_rn(v[1], v[3]), b2 = __fdiv_rn(v[2], v[3]);
         bad += (__float_as_uint(a0) != __float_as_uint(b0)) + (__float_as_uint(a1) != __float_as_uint(b1)) +
                (__float_as_uint(a2) != __float_as_uint(b2));
-        const float ad = fabsf(v[3]);
-        const float nmin = fminf(fminf(fabsf(v[0]), fabsf(v[1])), fabsf(v[2])), nmax = fmaxf(fmaxf(fabsf(v[0]), fabsf(v[1])), fabsf(v[2]));
-        fast += (ad >= 0x1p-40f && ad <= 0x1p40f && nmin >= ad * 0x1p-40f && nmax <= ad * 0x1p40f) ? 1u : 0u;
+        fast += div3_guard<false>(v[0], v[1], v[2], v[3]) ? 1u : 0u;
     }
     bad = __reduce_add_sync(0xFFFFFFFFu, static_cast<unsigned>(bad));
     fast = __reduce_add_sync(0xFFFFFFFFu, static_cast<unsigned>(fast));

@@ -184,10 +184,8 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
             float t, be, ga;
             if (STATS) ++myTris;
             if (LEAFREC || ROPES) {
-                uint32_t id;
-                if (tri_test<FASTREJ, DIV3>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, t, be, ga, &id)) {
-                    best = t; htri = id; hbeta = be; hgamma = ga;
-                }
+                // results written in place, inside the test's (rare) accept branch
+                tri_test<FASTREJ, DIV3>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, best, hbeta, hgamma, &htri);
             } else {
                 const uint32_t id = __ldg(p.sc.leaf_ids + li);
                 if (tri_test<FASTREJ, DIV3>(p.sc.tri_isect + 3 * id, ox, oy, oz, dx, dy, dz, best, t, be, ga)) {
