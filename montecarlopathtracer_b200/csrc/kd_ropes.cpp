@@ -13,7 +13,8 @@
 //
 //   rope_nodes  uint2 per node: inner = kd_nodes entry; leaf = {leaf ordinal, (count << 2) | 3}
 //   leaf_hdr    4 x float4 per leaf: {cell.lo, first record in leaf_tris} {cell.hi, count}
-//               {rope -x, +x, -y, +y} {rope -z, +z, -, -}   (node indices, 0xFFFFFFFF = outside the scene)
+//               {rope -x, +x, -y, +y} {rope -z, +z, -, -}   (0xFFFFFFFF = outside the scene; bit 31 set = the
+//               neighbour is one leaf: its ordinal in the low bits, no node to load; else a node index)
 #include <cstring>
 
 #include "device_scene.h"
@@ -23,6 +24,7 @@ namespace {
 
 inline float as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 const uint32_t kNone = 0xFFFFFFFFu;
+const uint32_t kRopeIsLeaf = 0x80000000u;  // same constant as MCPT_ROPE_IS_LEAF in intersect.cuh
 
 struct Cell {
     float lo[3], hi[3];
@@ -53,8 +55,13 @@ struct Builder {
             const uint32_t k = leafOrdinal[node];
             out.leaf_hdr[4 * k] = make_float4(cell.lo[0], cell.lo[1], cell.lo[2], as_float(out.kd_nodes[node].x));
             out.leaf_hdr[4 * k + 1] = make_float4(cell.hi[0], cell.hi[1], cell.hi[2], as_float(t.leaf_count[node]));
-            out.leaf_hdr[4 * k + 2] = make_float4(as_float(ropes[0]), as_float(ropes[1]), as_float(ropes[2]), as_float(ropes[3]));
-            out.leaf_hdr[4 * k + 3] = make_float4(as_float(ropes[4]), as_float(ropes[5]), 0.0f, 0.0f);
+            uint32_t enc[6];
+            for (int f = 0; f < 6; ++f) {
+                const uint32_t r = ropes[f];
+                enc[f] = (r != kNone && t.split_axis[r] == 0) ? (kRopeIsLeaf | leafOrdinal[r]) : r;
+            }
+            out.leaf_hdr[4 * k + 2] = make_float4(as_float(enc[0]), as_float(enc[1]), as_float(enc[2]), as_float(enc[3]));
+            out.leaf_hdr[4 * k + 3] = make_float4(as_float(enc[4]), as_float(enc[5]), 0.0f, 0.0f);
             return;
         }
         const int a = static_cast<int>(t.split_axis[node]) - 1;

@@ -153,8 +153,16 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     // tuning build: every kernel variant x residency for the headline combination (Philox, no NEE, no moments)
     if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
 #define MCPT_V(V) case V: render_kernel_sm<RNG, NEE, MOMENTS, 4, V><<<grid, 256, 0, stream>>>(p, r.shade_threshold); break;
-        if (r.variant == 23 && r.min_blocks == 5) { render_kernel_sm<RNG, NEE, MOMENTS, 5, 23><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
-        if (r.variant == 23 && r.min_blocks == 3) { render_kernel_sm<RNG, NEE, MOMENTS, 3, 23><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); }
+        if (r.variant == 55 && r.min_blocks == 8) {  // 128-thread blocks (16x8 tiles), 8 per SM
+            grid.y = (r.height + 7) / 8;
+            render_kernel_sm<RNG, NEE, MOMENTS, 8, 55, 128><<<grid, 128, 0, stream>>>(p, r.shade_threshold);
+            return cudaGetLastError();
+        }
+        if (r.variant == 55 && r.min_blocks == 16) {  // 64-thread blocks (16x4 tiles), 16 per SM
+            grid.y = (r.height + 3) / 4;
+            render_kernel_sm<RNG, NEE, MOMENTS, 16, 55, 64><<<grid, 64, 0, stream>>>(p, r.shade_threshold);
+            return cudaGetLastError();
+        }
         switch (r.variant) {
             MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20) MCPT_V(55) MCPT_V(53)
             default: return cudaErrorInvalidValue;

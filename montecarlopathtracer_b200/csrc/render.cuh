@@ -74,11 +74,12 @@ __device__ __forceinline__ Hit trace(const DScene& sc, F3 o, F3 d) {
     return intersect_ref(sc, o.x, o.y, o.z, d.x, d.y, d.z);
 }
 
-// Pixel of a thread: each warp covers an 8x4 tile, a 256-thread block a 16x16 tile.
+// Pixel of a thread: each warp covers an 8x4 tile, a block of BLOCK threads a 16 x (BLOCK/16) tile.
+template <int BLOCK = 256>
 __device__ __forceinline__ void thread_pixel(uint32_t& px, uint32_t& py) {
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     px = blockIdx.x * 16u + (warp & 1u) * 8u + (lane & 7u);
-    py = blockIdx.y * 16u + (warp >> 1) * 4u + (lane >> 3);
+    py = blockIdx.y * static_cast<uint32_t>(BLOCK / 16) + (warp >> 1) * 4u + (lane >> 3);
 }
 
 template <class RNG, bool KD, bool NEE, bool MOMENTS>

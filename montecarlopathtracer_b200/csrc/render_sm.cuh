@@ -28,15 +28,15 @@ enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 //   bit 4  camera-ray queue: the next sample's primary ray is generated ahead of time, for many lanes at once,
 //          and parked in shared memory (in-place generation runs with ~2.6 of 32 lanes);
 //   bit 5  div3_rn: the three IEEE quotients of a surviving triangle share one reciprocal and one range guard.
-template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR>
-__global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
+template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR, int BLOCK = 256>
+__global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
     constexpr bool LEAFREC = (VAR & 1) != 0, ROPES = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0, CAMQ = (VAR & 16) != 0,
                    DIV3 = (VAR & 32) != 0;
-    __shared__ float camq[CAMQ ? 7 * 256 : 1];  // CAMQ: parked primary ray {o, d, rng state} per thread
+    __shared__ float camq[CAMQ ? 7 * BLOCK : 1];  // CAMQ: parked primary ray {o, d, rng state} per thread
     bool camReady = false;
     uint32_t st[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
     uint32_t px, py;
-    thread_pixel(px, py);
+    thread_pixel<BLOCK>(px, py);
     const bool inside = px < static_cast<uint32_t>(p.width) && py < static_cast<uint32_t>(p.height);
     const uint32_t pixel = py * static_cast<uint32_t>(p.width) + px;
     const int chunk = blockIdx.z;
@@ -126,15 +126,15 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
             F3 o, d;
             camera_ray(p.cam, p.width, p.height, px, py, u1, u2, o, d);
             float* q = camq + threadIdx.x;
-            q[0] = o.x; q[256] = o.y; q[512] = o.z; q[768] = d.x; q[1024] = d.y; q[1280] = d.z;
-            q[1536] = __uint_as_float(r.save());
+            q[0] = o.x; q[BLOCK] = o.y; q[2 * BLOCK] = o.z; q[3 * BLOCK] = d.x; q[4 * BLOCK] = d.y; q[5 * BLOCK] = d.z;
+            q[6 * BLOCK] = __uint_as_float(r.save());
             camReady = true;
         }
     };
     auto take_parked_sample = [&]() {
         const float* q = camq + threadIdx.x;
-        ox = q[0]; oy = q[256]; oz = q[512]; dx = q[768]; dy = q[1024]; dz = q[1280];
-        rng.resume(pixel, p.seed, static_cast<uint32_t>(p.sample_begin + s), __float_as_uint(q[1536]));
+        ox = q[0]; oy = q[BLOCK]; oz = q[2 * BLOCK]; dx = q[3 * BLOCK]; dy = q[4 * BLOCK]; dz = q[5 * BLOCK];
+        rng.resume(pixel, p.seed, static_cast<uint32_t>(p.sample_begin + s), __float_as_uint(q[6 * BLOCK]));
         thr = f3(1, 1, 1); cur = f3(0, 0, 0);
         bounce = 0; lastWasNee = false; shadow = false;
         camReady = false;
@@ -330,11 +330,15 @@ __global__ void __launch_bounds__(256, MIN_BLOCKS) render_kernel_sm(const Render
                         state = ST_SHADE;
                     } else {
                         tmin = fmaxf(tmin, e.t);
-                        float qx = ox + tmin * dx, qy = oy + tmin * dy, qz = oz + tmin * dz;
-                        if (e.axis == 0u) qx = e.plane;
-                        if (e.axis == 1u) qy = e.plane;
-                        if (e.axis == 2u) qz = e.plane;
-                        leaf = rope_locate(p.sc, e.rope, qx, qy, qz, nearBits);
+                        if (e.rope & MCPT_ROPE_IS_LEAF) {
+                            leaf = e.rope & ~MCPT_ROPE_IS_LEAF;  // one leaf behind the whole face: nothing to locate
+                        } else {
+                            float qx = ox + tmin * dx, qy = oy + tmin * dy, qz = oz + tmin * dz;
+                            if (e.axis == 0u) qx = e.plane;
+                            if (e.axis == 1u) qy = e.plane;
+                            if (e.axis == 2u) qz = e.plane;
+                            leaf = rope_locate(p.sc, e.rope, qx, qy, qz, nearBits);
+                        }
                     }
                 }
             } else if (state == ST_INNER) {
