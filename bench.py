@@ -325,8 +325,8 @@ def main():
     line["roofline"] = {"bound": "hbm", "achieved": abytes / t_launch / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": abytes / t_launch / 1e9 / hbm_peak,
                         # dram__bytes_read.sum + dram__bytes_write.sum of ONE render_kernel_sm launch at the K2 size
-                        # (profiles/r1d_ncu_full_render_kernel_sm_K2_raw.csv); other workloads were not captured
-                        "traffic": 1550848 if (args.workload == "K2" and not args.spp) else None,
+                        # (profiles/r1f_ncu_full_render_kernel_sm_K2_raw.csv; the four 16 MB accumulation slices mostly stay in L2); other workloads were not captured
+                        "traffic": 19752448 if (args.workload == "K2" and not args.spp) else None,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                         "kernel": "render_kernel_sm", "launch_ms": t_launch * 1e3,
                         "algorithmic_bytes_per_ray": nn * B_NODE + nt * B_TRI, "algorithmic_flops_per_ray": nn * F_NODE + nt * F_TRI,
