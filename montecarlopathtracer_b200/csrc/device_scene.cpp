@@ -51,6 +51,7 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     }
     out.ref_nodes.resize(2 * nN);
     out.kd_nodes.resize(nN);
+#pragma omp parallel for schedule(static) if (nN > 65536)
     for (size_t k = 0; k < nN; ++k) {
         const float* bb = &tree.aabb[6 * k];
         uint32_t a, b, kx, ky;
@@ -77,6 +78,7 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     out.emitters.clear();
     double areaSum = 0.0;
     std::vector<double> areas;
+#pragma omp parallel for schedule(static) if (nT > 65536)
     for (size_t t = 0; t < nT; ++t) {
         const uint32_t* r = &scene.triangles[7 * t];
         const float* a = &scene.vertices[3 * static_cast<size_t>(r[0])];
@@ -94,6 +96,12 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         out.tri_shade[3 * t] = make_float4(n0[0], n0[1], n0[2], as_float(r[6]));
         out.tri_shade[3 * t + 1] = make_float4(n1[0], n1[1], n1[2], 0.0f);
         out.tri_shade[3 * t + 2] = make_float4(n2[0], n2[1], n2[2], 0.0f);
+    }
+    for (size_t t = 0; t < nT; ++t) {  // emitters keep triangle order: sequential
+        const uint32_t* r = &scene.triangles[7 * t];
+        const float* a = &scene.vertices[3 * static_cast<size_t>(r[0])];
+        const float* b = &scene.vertices[3 * static_cast<size_t>(r[1])];
+        const float* c = &scene.vertices[3 * static_cast<size_t>(r[2])];
         // Emitter iff any Ka component > 0 (rtx.hlsl:330).
         const float* Ka = &scene.materials[12 * static_cast<size_t>(r[6])];
         if (Ka[0] > 0 || Ka[1] > 0 || Ka[2] > 0) {
@@ -109,6 +117,7 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         }
     }
     out.leaf_tris.resize(3 * out.leaf_ids.size());
+#pragma omp parallel for schedule(static) if (out.leaf_ids.size() > 65536)
     for (size_t k = 0; k < out.leaf_ids.size(); ++k)
         for (int j = 0; j < 3; ++j) out.leaf_tris[3 * k + j] = out.tri_isect[3 * static_cast<size_t>(out.leaf_ids[k]) + j];
 
