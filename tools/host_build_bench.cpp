@@ -34,7 +34,7 @@ int main(int argc, char** argv) {
     auto secs = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
     HostTree tree;
     auto t0 = now();
-    build_kd_tree(s, 1 /* MCPT_BUILD_SAH */, tree);
+    build_kd_tree(s, argc > 2 ? std::atoi(argv[2]) : 1 /* 1 = MCPT_BUILD_SAH, 0 = reference rule */, tree);
     auto t1 = now();
     PackedScene packed;
     pack_scene(s, tree, packed);
