@@ -206,6 +206,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
             if (STATS) { st[7] += 1; st[8] += __popc(__ballot_sync(0xFFFFFFFFu, state == ST_SHADE)); }
             if (state == ST_SHADE) {
                 bool done = false, haveRay = false;
+                // Without NEE a path's only contribution is the emitter it ends on: `cur` is zero until the shading
+                // event that ends the path, so it need not live in a register between events.
+                if (!NEE) cur = f3(0, 0, 0);
                 if (NEE && shadow) {
                     if (htri == shTri) cur = cur + shVal;  // the sampled emitter point is visible
                     shadow = false;
