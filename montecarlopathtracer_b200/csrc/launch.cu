@@ -10,7 +10,7 @@
 
 // Shipping configuration of the persistent-lane kernel (profiles/r1_tuning.md).
 #ifndef MCPT_SM_VARIANT
-#define MCPT_SM_VARIANT 55
+#define MCPT_SM_VARIANT 119
 #endif
 #ifndef MCPT_SM_MIN_BLOCKS
 #define MCPT_SM_MIN_BLOCKS 4
@@ -134,7 +134,7 @@ cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
-    p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = 16;
+    p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = 16; p.tri_cap = 4;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
     render_kernel<RNG, KD, NEE, MOMENTS><<<grid, 256, 0, stream>>>(p);
@@ -146,7 +146,7 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
-    p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = r.cam_threshold;
+    p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = r.cam_threshold; p.tri_cap = r.tri_cap;
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
 #ifdef MCPT_TUNE
@@ -164,7 +164,7 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
             return cudaGetLastError();
         }
         switch (r.variant) {
-            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20) MCPT_V(55) MCPT_V(53)
+            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20) MCPT_V(55) MCPT_V(53) MCPT_V(119)
             default: return cudaErrorInvalidValue;
         }
 #undef MCPT_V

@@ -26,6 +26,7 @@ struct RenderLaunch {
     int min_blocks;        // tuning builds only: 2, 3 or 4 resident 256-thread blocks per SM (register cap 128 / 85 / 64)
     int variant;           // tuning builds only: VAR bits of render_kernel_sm
     int cam_threshold;     // camera-ray queue refill threshold (lanes)
+    int tri_cap;           // triangle tests per lane and round (VAR bit 6)
 };
 
 // Number of kernels launched is returned through *launches (adds to it).

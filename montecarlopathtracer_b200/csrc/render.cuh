@@ -26,6 +26,7 @@ struct RenderParams {
     uint32_t seed;
     uint32_t jitter;
     int cam_threshold;     // render_kernel_sm, camera-ray queue: lanes that must need a refill before the warp refills
+    int tri_cap;           // render_kernel_sm, VAR bit 6: triangle tests per lane and round
     float emission_scale;
     float4* sum;           // [chunks][height][width]  r,g,b sums + sample count
     float4* sumsq;         // same layout, or nullptr

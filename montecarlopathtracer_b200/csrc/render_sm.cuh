@@ -27,11 +27,13 @@ enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 //   bit 2  tri_test<true> (division-free rejections, intersect.cuh);
 //   bit 4  camera-ray queue: the next sample's primary ray is generated ahead of time, for many lanes at once,
 //          and parked in shared memory (in-place generation runs with ~2.6 of 32 lanes);
-//   bit 5  div3_rn: the three IEEE quotients of a surviving triangle share one reciprocal and one range guard.
+//   bit 5  div3_rn: the three IEEE quotients of a surviving triangle share one reciprocal and one range guard;
+//   bit 6  (with bit 1) at most `tri_cap` triangle tests per lane and round: a lane in a bigger leaf stays in it
+//          (ST_LEAF) and goes on next round, so the round's triangle loop is not as long as the warp's biggest leaf.
 template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR, int BLOCK = 256>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
     constexpr bool LEAFREC = (VAR & 1) != 0, ROPES = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0, CAMQ = (VAR & 16) != 0,
-                   DIV3 = (VAR & 32) != 0;
+                   DIV3 = (VAR & 32) != 0, TRICAP = ROPES && (VAR & 64) != 0;
     __shared__ float camq[CAMQ ? 7 * BLOCK : 1];  // CAMQ: parked primary ray {o, d, rng state} per thread
     bool camReady = false;
     uint32_t st[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
@@ -179,8 +181,8 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         }
         li = n.x; lend = n.x + (n.y >> 2);
     };
-    auto test_leaf = [&]() {
-        for (; li < lend; ++li) {
+    auto test_leaf = [&](uint32_t stop) {
+        for (; li < stop; ++li) {
             float t, be, ga;
             if (STATS) ++myTris;
             if (LEAFREC || ROPES) {
@@ -319,10 +321,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         while (true) {
             if (STATS) { myNodes = 0; myTris = 0; st[1] += 1; st[2] += __popc(__ballot_sync(0xFFFFFFFFu, state == ST_INNER)); }
             if (ROPES) {
+                if (state == ST_INNER || (TRICAP && state == ST_LEAF)) {
+                    const float4 h0 = ldg4(p.sc.leaf_hdr + 4 * leaf), h1 = ldg4(p.sc.leaf_hdr + 4 * leaf + 1);
+                    if (!TRICAP || state == ST_INNER) { li = __float_as_uint(h0.w); lend = li + __float_as_uint(h1.w); }
+                    test_leaf(TRICAP ? min(lend, li + static_cast<uint32_t>(p.tri_cap)) : lend);
+                    if (TRICAP) state = li < lend ? ST_LEAF : ST_INNER;
+                }
                 if (state == ST_INNER) {
                     const float4 h0 = ldg4(p.sc.leaf_hdr + 4 * leaf), h1 = ldg4(p.sc.leaf_hdr + 4 * leaf + 1);
-                    li = __float_as_uint(h0.w); lend = li + __float_as_uint(h1.w);
-                    test_leaf();
                     const LeafExit e = leaf_exit(p.sc, leaf, h0, h1, ox, oy, oz, ix, iy, iz, nearBits);
                     // No hop counter here (it costs a register the kernel does not have; intersect_ropes keeps one):
                     // the walk terminates structurally.  The face taken on each axis is fixed by the ray's sign bits,
@@ -346,14 +352,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                 }
             } else if (state == ST_INNER) {
                 descend();
-                test_leaf();
+                test_leaf(lend);
                 pop_or_finish();
             }
             if (STATS) {
                 st[3] += __reduce_add_sync(0xFFFFFFFFu, myNodes); st[4] += __reduce_max_sync(0xFFFFFFFFu, myNodes);
                 st[5] += __reduce_add_sync(0xFFFFFFFFu, myTris); st[6] += __reduce_max_sync(0xFFFFFFFFu, myTris);
             }
-            if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER)) >= shadeThreshold) break;
+            if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER && state != ST_LEAF)) >= shadeThreshold) break;
         }
     }
 
