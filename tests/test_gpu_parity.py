@@ -227,6 +227,39 @@ def test_render_sample_ranges_and_device_accumulation(gpu, scenes):
     assert np.array_equal(T.render_scene(T.render_cfg(W, H, 12, 8, seed=3)), full)
 
 
+def test_full_size_k2_properties(gpu, oracle, scenes, monkeypatch):
+    """BASELINE.json configs[1] at its full size (1024x1024, 1024 spp, depth 8: 1.07 G paths), through properties that
+    do not need an oracle render of that size: (i) the estimate does not depend on how the spp are cut into launch
+    slices; (ii) two disjoint halves of the sample range sum to the whole (what the multi-GPU split relies on);
+    (iii) finite, non-negative, deterministic; (iv) mean radiance and rays per path agree with the oracle's own
+    render of the same pixels at 4 spp (same estimator, independent samples: within Monte Carlo error)."""
+    T, s = gpu, scenes["scene01_lambert"]
+    _load(T, s, T.BUILD_SAH)
+    W = H = 1024
+    spp = 1024
+    full = T.render_scene(T.render_cfg(W, H, spp, 8, seed=11))
+    c = T.counters()
+    assert c.paths == W * H * spp
+    rays_per_path = c.rays / c.paths
+    assert np.isfinite(full).all() and (full >= 0).all() and full.max() > 0
+    assert np.array_equal(T.render_scene(T.render_cfg(W, H, spp, 8, seed=11)), full)
+    # (i) one slice per tile instead of pick_chunks' four
+    monkeypatch.setenv("MCPT_CHUNKS", "1")
+    one = T.render_scene(T.render_cfg(W, H, spp, 8, seed=11))
+    monkeypatch.delenv("MCPT_CHUNKS")
+    assert np.allclose(one, full, rtol=2e-5, atol=1e-7)
+    # (ii) halves
+    a = T.render_scene(T.render_cfg(W, H, spp // 2, 8, seed=11, sample_offset=0))
+    b = T.render_scene(T.render_cfg(W, H, spp // 2, 8, seed=11, sample_offset=spp // 2))
+    assert np.allclose(0.5 * (a.astype(np.float64) + b), full, rtol=2e-5, atol=1e-7)
+    # (iv) the oracle at 4 spp: 4.2 M paths
+    ocfg = oracle.cfg(W, H, 4, 8, rng_mode=1, seed=5, eye=(0, 5, 17), at=(0, 5, 16))
+    osum, _, _, ocnt = oracle.scene(s).render(ocfg)
+    o_mean = osum.mean() / 4
+    assert abs(full.astype(np.float64).mean() - o_mean) / o_mean < 0.01      # the north_star's 1 % gate
+    assert abs(rays_per_path - ocnt.rays / ocnt.paths) / rays_per_path < 0.005
+
+
 @pytest.mark.parametrize("flags", [0, 1])
 def test_kernel_variants_render_identical_images(gpu, scenes, flags):
     """The warp-voted state machine, the one-ray-per-iteration kernel and the reference-order traversal
