@@ -343,6 +343,34 @@ def test_tessellated_surface_scene(gpu, oracle, scenes):
         assert np.isclose(mean, osum / spp, rtol=1e-3, atol=1e-5).all(-1).mean() > 0.97
 
 
+def test_full_size_k4_traversals_agree(gpu, scenes):
+    """BASELINE.json configs[3] at its full size (1 002 550 triangles; the oracle's reference tree alone takes 25 s
+    there), through cross-checks between independent pieces of this library: the reference-order AABB
+    traversal of the reference-rule tree, the stack traversal and the stackless walk of the SAH tree must report the
+    same closest hit (id equal, t bit-equal) for camera rays and for rays with origins all over the scene, and the
+    render of the full configuration is finite, non-negative and lit."""
+    from montecarlopathtracer_b200 import scenes as S
+    from oracle.pyoracle import SceneArrays
+    T, b = gpu, scenes["scene01_lambert"]
+    s = SceneArrays(*S.cornell_heightfield((b.verts, b.normals, b.tris, b.mats), 708))
+    assert len(s.tris) == 22 + 2 * 708 * 708
+    _load(T, s, T.BUILD_REFERENCE)
+    rays = np.concatenate([T.primary_rays(T.render_cfg(256, 256, 1, 8, jitter=0), 0).reshape(-1, 6), _random_rays(s, 1 << 18, seed=9)])
+    rtri, rt, _, _ = T.intersect_batch(rays, T.ISECT_REFERENCE)
+    assert (rtri >= 22).mean() > 0.15
+    _load(T, s, T.BUILD_SAH)
+    for variant in (T.ISECT_KD, T.ISECT_ROPES):
+        ktri, kt, _, _ = T.intersect_batch(rays, variant)
+        bad = (ktri != rtri) | ((rtri >= 0) & (_bits(kt) != _bits(rt)))
+        # the reference-order slab test drops a real hit through rounding for a few rays in 10^5 (DESIGN.md 3.2);
+        # where the two differ the KD result must be the closer hit
+        assert bad.mean() <= 1e-4, bad.mean()
+        assert (kt[bad & (ktri >= 0) & (rtri >= 0)] <= rt[bad & (ktri >= 0) & (rtri >= 0)]).all()
+    img = T.render_scene(T.render_cfg(1024, 1024, 256, 8, seed=2))
+    assert T.counters().paths == 1024 * 1024 * 256
+    assert np.isfinite(img).all() and (img >= 0).all() and img.max() > 0 and img.mean() > 1e-4, float(img.mean())
+
+
 TWIN_FOVY = np.float32(60) * np.float32(3.14159265359) / np.float32(180)
 
 
