@@ -32,7 +32,7 @@ cudaError_t upload(DeviceBuffer<T>& dst, const std::vector<T>& src, cudaStream_t
 }
 
 void release_device_scene(Context& c) {
-    c.d_ref_nodes.release(); c.d_kd_nodes.release(); c.d_leaf_ids.release(); c.d_tri_isect.release(); c.d_leaf_tris.release(); c.d_leaf_hdr.release(); c.d_rope_nodes.release();
+    c.d_ref_nodes.release(); c.d_kd_nodes.release(); c.d_leaf_ids.release(); c.d_tri_isect.release(); c.d_leaf_tris.release(); c.d_leaf_blob.release(); c.d_rope_nodes.release();
     c.d_tri_shade.release(); c.d_mats.release(); c.d_emitters.release();
     c.uploaded = false;
 }
@@ -44,7 +44,7 @@ int install_scene(HostScene&& scene, int build_mode) {
     if (!validate_scene(scene, err)) return fail(MCPT_ERR_INVALID, err);
     c.scene = std::move(scene);
     build_kd_tree(c.scene, build_mode, c.tree);
-    pack_scene(c.scene, c.tree, c.packed);
+    if (!pack_scene(c.scene, c.tree, c.packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
     c.has_geometry = true;
     c.uploaded = false;
     if (c.has_device) return ensure_uploaded();
@@ -65,7 +65,7 @@ int ensure_uploaded() {
     if ((e = upload(c.d_leaf_ids, c.packed.leaf_ids, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_ids");
     if ((e = upload(c.d_tri_isect, c.packed.tri_isect, c.stream)) != cudaSuccess) return fail_cuda(e, "upload tri_isect");
     if ((e = upload(c.d_leaf_tris, c.packed.leaf_tris, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_tris");
-    if ((e = upload(c.d_leaf_hdr, c.packed.leaf_hdr, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_hdr");
+    if ((e = upload(c.d_leaf_blob, c.packed.leaf_blob, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_blob");
     if ((e = upload(c.d_rope_nodes, c.packed.rope_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload rope_nodes");
     if ((e = upload(c.d_tri_shade, c.packed.tri_shade, c.stream)) != cudaSuccess) return fail_cuda(e, "upload tri_shade");
     if ((e = upload(c.d_mats, c.packed.mats, c.stream)) != cudaSuccess) return fail_cuda(e, "upload mats");
@@ -73,7 +73,7 @@ int ensure_uploaded() {
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "scene upload");
     DScene& d = c.dscene;
     d.ref_nodes = c.d_ref_nodes.ptr; d.kd_nodes = c.d_kd_nodes.ptr; d.leaf_ids = c.d_leaf_ids.ptr;
-    d.tri_isect = c.d_tri_isect.ptr; d.leaf_tris = c.d_leaf_tris.ptr; d.rope_nodes = c.d_rope_nodes.ptr; d.leaf_hdr = c.d_leaf_hdr.ptr; d.tri_shade = c.d_tri_shade.ptr; d.mats = c.d_mats.ptr; d.emitters = c.d_emitters.ptr;
+    d.tri_isect = c.d_tri_isect.ptr; d.leaf_tris = c.d_leaf_tris.ptr; d.rope_nodes = c.d_rope_nodes.ptr; d.leaf_blob = c.d_leaf_blob.ptr; d.tri_shade = c.d_tri_shade.ptr; d.mats = c.d_mats.ptr; d.emitters = c.d_emitters.ptr;
     for (int i = 0; i < 3; ++i) { d.bmin[i] = c.packed.bmin[i]; d.bmax[i] = c.packed.bmax[i]; }
     d.num_nodes = static_cast<uint32_t>(c.tree.num_nodes());
     d.num_tris = static_cast<uint32_t>(c.scene.num_triangles());

@@ -42,7 +42,7 @@ struct Context {
     HostTree tree;
     PackedScene packed;
     DScene dscene{};
-    DeviceBuffer<float4> d_ref_nodes, d_tri_isect, d_leaf_tris, d_leaf_hdr, d_tri_shade, d_mats, d_emitters;
+    DeviceBuffer<float4> d_ref_nodes, d_tri_isect, d_leaf_tris, d_leaf_blob, d_tri_shade, d_mats, d_emitters;
     DeviceBuffer<uint2> d_kd_nodes, d_rope_nodes;
     DeviceBuffer<uint32_t> d_leaf_ids;
 

@@ -14,7 +14,7 @@ inline float as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 inline uint32_t as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 }  // namespace
 
-void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) {
+bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) {
     const size_t nN = tree.num_nodes(), nT = scene.num_triangles(), nM = scene.num_materials();
     // Device order of the leaves: depth first (left subtree first), so that the id lists, triangle records and
     // headers of spatially neighbouring leaves are neighbours in memory (the host tree keeps the reference's
@@ -121,7 +121,7 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     for (size_t k = 0; k < out.leaf_ids.size(); ++k)
         for (int j = 0; j < 3; ++j) out.leaf_tris[3 * k + j] = out.tri_isect[3 * static_cast<size_t>(out.leaf_ids[k]) + j];
 
-    build_ropes(tree, out);
+    const bool ropesOk = build_ropes(tree, out);
 
     // running CDF over emitter area for area-uniform light sampling
     double run = 0.0;
@@ -139,6 +139,7 @@ void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         out.mats[3 * m + 1] = make_float4(p[3], p[4], p[5], p[10]);  // Kd, Tr
         out.mats[3 * m + 2] = make_float4(p[6], p[7], p[8], p[11]);  // Ks, Ni
     }
+    return ropesOk;
 }
 
 // D3DXMatrixLookAtRH / Inverse / PerspectiveFovRH in closed form (GraphicsRTX.cpp:173-184):

@@ -18,7 +18,7 @@
 //   leaf_tris  3 x float4 per LEAF REFERENCE: the tri_isect record of leaf_ids[k] copied in place k, with the
 //                 triangle id in the free lane {e1.xyz, id bits}: a leaf's triangles are consecutive 48-byte
 //                 records and the render path needs no id -> record indirection (tuning build variant)
-//   rope_nodes, leaf_hdr   stackless traversal: see kd_ropes.cpp
+//   rope_nodes, leaf_blob  stackless traversal: see kd_ropes.cpp
 //   tri_shade  3 x float4 per triangle {n0.xyz, matId bits} {n1.xyz, 0} {n2.xyz, 0}
 //   mats       3 x float4 per material {Ka, Ns} {Kd, Tr} {Ks, Ni}
 //   emitters   3 x float4 per emitting triangle {a.xyz, area} {b-a, cdf} {c-a, triangle id bits}
@@ -39,7 +39,7 @@ struct DScene {
     const float4* tri_isect;
     const float4* leaf_tris;
     const uint2* rope_nodes;
-    const float4* leaf_hdr;
+    const float4* leaf_blob;
     const float4* tri_shade;
     const float4* mats;
     const float4* emitters;
@@ -62,17 +62,17 @@ struct PackedScene {
     std::vector<uint2> kd_nodes, rope_nodes;
     std::vector<uint32_t> leaf_ids;
     std::vector<uint32_t> leaf_order;  // per node: depth-first ordinal of a leaf (host only)
-    std::vector<float4> tri_isect, leaf_tris, leaf_hdr, tri_shade, mats, emitters;
+    std::vector<float4> tri_isect, leaf_tris, leaf_blob, tri_shade, mats, emitters;
     float bmin[3], bmax[3];
     float emitter_area = 0.0f;
     size_t bytes() const {
         return ref_nodes.size() * 16 + (kd_nodes.size() + rope_nodes.size()) * 8 + leaf_ids.size() * 4 +
-               (tri_isect.size() + leaf_tris.size() + leaf_hdr.size() + tri_shade.size() + mats.size() + emitters.size()) * 16;
+               (tri_isect.size() + leaf_tris.size() + leaf_blob.size() + tri_shade.size() + mats.size() + emitters.size()) * 16;
     }
 };
 
-void pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out);
-void build_ropes(const HostTree& tree, PackedScene& out);  // kd_ropes.cpp; needs kd_nodes of pack_scene
+bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out);  // false: scene too large for the leaf-block layout
+bool build_ropes(const HostTree& tree, PackedScene& out);  // kd_ropes.cpp; needs kd_nodes, leaf_tris of pack_scene; false: too many leaf references
 DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height, int twin = 0);
 
 }  // namespace mcpt

@@ -11,10 +11,16 @@
 // Cells are derived from the split planes alone (root cell = root box), so this works for both builders:
 // the reference-rule tree stores CLIPPED boxes per node (KDTree.hpp:154-155), which are not a partition.
 //
-//   rope_nodes  uint2 per node: inner = kd_nodes entry; leaf = {leaf ordinal, (count << 2) | 3}
-//   leaf_hdr    4 x float4 per leaf: {cell.lo, first record in leaf_tris} {cell.hi, count}
-//               {rope -x, +x, -y, +y} {rope -z, +z, -, -}   (0xFFFFFFFF = outside the scene; bit 31 set = the
-//               neighbour is one leaf: its ordinal in the low bits, no node to load; else a node index)
+//   leaf_blob   one block per leaf, leaves in depth-first order: 4 x float4 of header
+//               {cell.lo, first slot in leaf_ids} {cell.hi, count} {rope -x, +x, -y, +y} {rope -z, +z, -, -}
+//               followed by the leaf's `count` triangle records (3 x float4 each, the leaf_tris records).  A leaf is
+//               named by its HANDLE: bits 0-27 = offset of the block in float4 units, bits 28-30 = min(count, 7).
+//               With the handle alone a ray knows where the triangle records are and (for all but leaves of 7+
+//               triangles) how many: the triangle tests do not wait for the header, which is only needed for the
+//               exit face afterwards -- one dependent memory round trip less per leaf visit.
+//               A rope is 0xFFFFFFFF = outside the scene; bit 31 set = the neighbour is one leaf: its handle in the
+//               low bits, no node to load; else a node index.
+//   rope_nodes  uint2 per node: inner = kd_nodes entry; leaf = {leaf handle, (count << 2) | 3}
 #include <cstring>
 
 #include "device_scene.h"
@@ -24,7 +30,8 @@ namespace {
 
 inline float as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 const uint32_t kNone = 0xFFFFFFFFu;
-const uint32_t kRopeIsLeaf = 0x80000000u;  // same constant as MCPT_ROPE_IS_LEAF in intersect.cuh
+const uint32_t kRopeIsLeaf = 0x80000000u;      // same constants as MCPT_ROPE_IS_LEAF, MCPT_LEAF_OFF, MCPT_LEAF_CNT in intersect.cuh
+const uint32_t kLeafOffsetMask = 0x0FFFFFFFu;
 
 struct Cell {
     float lo[3], hi[3];
@@ -33,7 +40,7 @@ struct Cell {
 struct Builder {
     const HostTree& t;
     PackedScene& out;
-    std::vector<uint32_t> leafOrdinal;
+    std::vector<uint32_t> leafHandle;  // per node (leaves only)
 
     // Pushes rope `r` of a face (axis fa, min side if !maxSide) of `cell` down to the deepest node that still
     // covers the whole face.
@@ -52,16 +59,18 @@ struct Builder {
 
     void walk(uint32_t node, const Cell& cell, const uint32_t ropes[6]) {
         if (t.split_axis[node] == 0) {
-            const uint32_t k = leafOrdinal[node];
-            out.leaf_hdr[4 * k] = make_float4(cell.lo[0], cell.lo[1], cell.lo[2], as_float(out.kd_nodes[node].x));
-            out.leaf_hdr[4 * k + 1] = make_float4(cell.hi[0], cell.hi[1], cell.hi[2], as_float(t.leaf_count[node]));
+            float4* blk = out.leaf_blob.data() + (leafHandle[node] & kLeafOffsetMask);
+            const uint32_t first = out.kd_nodes[node].x, count = t.leaf_count[node];
+            blk[0] = make_float4(cell.lo[0], cell.lo[1], cell.lo[2], as_float(first));
+            blk[1] = make_float4(cell.hi[0], cell.hi[1], cell.hi[2], as_float(count));
             uint32_t enc[6];
             for (int f = 0; f < 6; ++f) {
                 const uint32_t r = ropes[f];
-                enc[f] = (r != kNone && t.split_axis[r] == 0) ? (kRopeIsLeaf | leafOrdinal[r]) : r;
+                enc[f] = (r != kNone && t.split_axis[r] == 0) ? (kRopeIsLeaf | leafHandle[r]) : r;
             }
-            out.leaf_hdr[4 * k + 2] = make_float4(as_float(enc[0]), as_float(enc[1]), as_float(enc[2]), as_float(enc[3]));
-            out.leaf_hdr[4 * k + 3] = make_float4(as_float(enc[4]), as_float(enc[5]), 0.0f, 0.0f);
+            blk[2] = make_float4(as_float(enc[0]), as_float(enc[1]), as_float(enc[2]), as_float(enc[3]));
+            blk[3] = make_float4(as_float(enc[4]), as_float(enc[5]), 0.0f, 0.0f);
+            for (uint32_t k = 0; k < 3 * count; ++k) blk[4 + k] = out.leaf_tris[3 * static_cast<size_t>(first) + k];
             return;
         }
         const int a = static_cast<int>(t.split_axis[node]) - 1;
@@ -85,22 +94,32 @@ struct Builder {
 
 }  // namespace
 
-void build_ropes(const HostTree& tree, PackedScene& out) {
+bool build_ropes(const HostTree& tree, PackedScene& out) {
     const size_t nN = tree.num_nodes();
     Builder b{tree, out, std::vector<uint32_t>(nN, 0u)};
-    uint32_t leaves = 0;
-    out.rope_nodes = out.kd_nodes;
+    // blocks in depth-first leaf order (pack_scene's leaf_order): offsets by a prefix sum over the ordinals
+    std::vector<uint32_t> nodeOfOrdinal;
     for (size_t k = 0; k < nN; ++k)
         if (tree.split_axis[k] == 0) {
-            b.leafOrdinal[k] = out.leaf_order[k];  // depth-first ordinal (pack_scene)
-            out.rope_nodes[k].x = out.leaf_order[k];
-            ++leaves;
+            if (out.leaf_order[k] >= nodeOfOrdinal.size()) nodeOfOrdinal.resize(out.leaf_order[k] + 1u, 0u);
+            nodeOfOrdinal[out.leaf_order[k]] = static_cast<uint32_t>(k);
         }
-    out.leaf_hdr.assign(4 * static_cast<size_t>(leaves), make_float4(0, 0, 0, 0));
+    out.rope_nodes = out.kd_nodes;
+    size_t units = 0;
+    for (const uint32_t k : nodeOfOrdinal) {
+        if (units >= kLeafOffsetMask) return false;  // 4 GiB of leaf blocks: the 28-bit offset is exhausted
+        const uint32_t count = tree.leaf_count[k];
+        b.leafHandle[k] = static_cast<uint32_t>(units) | ((count < 7u ? count : 7u) << 28);
+        out.rope_nodes[k].x = b.leafHandle[k];
+        units += 4u + 3u * static_cast<size_t>(count);
+    }
+    // three float4 of padding: a lane may read one record past a leaf of 7+ triangles' known count, never past this
+    out.leaf_blob.assign(units + 3, make_float4(0, 0, 0, 0));
     Cell root;
     for (int i = 0; i < 3; ++i) { root.lo[i] = tree.aabb[i]; root.hi[i] = tree.aabb[3 + i]; }
     const uint32_t none[6] = {kNone, kNone, kNone, kNone, kNone, kNone};
     b.walk(0u, root, none);
+    return true;
 }
 
 }  // namespace mcpt

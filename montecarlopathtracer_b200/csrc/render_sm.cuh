@@ -66,7 +66,16 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
 
     // Prepares traversal of the ray (ox..dz): reciprocal, child order bits, clip against the root box.
     auto begin_ray = [&]() {
-        ix = __frcp_rn(dx); iy = __frcp_rn(dy); iz = __frcp_rn(dz);  // correctly rounded 1/d, same bits as 1.0f / d
+        // 1/d steers the walk only (which cells, when to stop); hits are computed from o and d.  The stackless walk needs
+        // no more than the hardware reciprocal (<= 1 ulp, 3 instructions instead of ~30 for three IEEE reciprocals);
+        // the stack traversal keeps the correctly rounded one.
+        if (ROPES) {
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ix) : "f"(dx));
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iy) : "f"(dy));
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(iz) : "f"(dz));
+        } else {
+            ix = __frcp_rn(dx); iy = __frcp_rn(dy); iz = __frcp_rn(dz);
+        }
         nearBits = (ix < 0.0f ? 1u : 0u) | (iy < 0.0f ? 2u : 0u) | (iz < 0.0f ? 4u : 0u);
         tmin = 0.0f; tmax = 10000.0f;
         float tn = (p.sc.bmin[0] - ox) * ix, tf = (p.sc.bmax[0] - ox) * ix;
@@ -81,7 +90,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         tmin *= (1.0f - 4e-7f); tmax *= (1.0f + 4e-7f);
         best = 10000.0f; htri = 0xFFFFFFFFu; hbeta = 0; hgamma = 0;
         node = 0; top = 0;
-        ++nrays;
         state = (tmin <= tmax) ? ST_INNER : ST_SHADE;  // a ray that misses the scene box is shaded as a miss
         if (ROPES && state == ST_INNER) {
             // tmin doubles as the distance already covered.  The walk starts in the leaf that contains the
@@ -98,7 +106,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
             }
             bool located = false;
             if (hint != 0xFFFFFFFFu) {
-                const float4 h0 = ldg4(p.sc.leaf_hdr + 4 * hint), h1 = ldg4(p.sc.leaf_hdr + 4 * hint + 1);
+                const float4 h0 = ldg4(p.sc.leaf_blob + MCPT_LEAF_OFF(hint)), h1 = ldg4(p.sc.leaf_blob + MCPT_LEAF_OFF(hint) + 1);
                 located = qx >= h0.x && qx <= h1.x && qy >= h0.y && qy <= h1.y && qz >= h0.z && qz <= h1.z;
             }
             if (STATS) { st[3] += 1; st[4] += located ? 1u : 0u; }
@@ -182,11 +190,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         li = n.x; lend = n.x + (n.y >> 2);
     };
     auto test_leaf = [&](uint32_t stop) {
-        for (; li < stop; ++li) {
+        for (; li < stop; li += ROPES ? 3u : 1u) {
             float t, be, ga;
             if (STATS) ++myTris;
-            if (LEAFREC || ROPES) {
-                // results written in place, inside the test's (rare) accept branch
+            if (ROPES) {
+                // li walks the leaf's block in float4 units; results written in place, inside the test's (rare) accept branch
+                tri_test<FASTREJ, DIV3>(p.sc.leaf_blob + li, ox, oy, oz, dx, dy, dz, best, best, hbeta, hgamma, &htri);
+            } else if (LEAFREC) {
                 tri_test<FASTREJ, DIV3>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, best, hbeta, hgamma, &htri);
             } else {
                 const uint32_t id = __ldg(p.sc.leaf_ids + li);
@@ -284,6 +294,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                                         const float g = cosx * cosy * p.sc.emitter_area / (MCPT_PI * r2);
                                         shVal = thr * f3(lKa.x, lKa.y, lKa.z) * (g * p.emission_scale);
                                         shadow = true;
+                                        ++nrays;
                                         nextOrg = hp + dir * 0.01f;  // the path ray waits behind the shadow ray
                                         nextDir = dir;
                                         const F3 so = hp + w * 0.01f;
@@ -303,6 +314,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                 }
                 if (STATS && done) st[9] += 1;
                 if (done) {
+                    nrays += bounce + 1u;  // the camera ray and one ray per scattering event (shadow rays are counted where they start)
                     acc = acc + cur;
                     if (MOMENTS) acc2 = acc2 + cur * cur;
                     ++s;
@@ -321,15 +333,21 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         while (true) {
             if (STATS) { myNodes = 0; myTris = 0; st[1] += 1; st[2] += __popc(__ballot_sync(0xFFFFFFFFu, state == ST_INNER)); }
             if (ROPES) {
+                // The leaf's handle says where its block is and (up to 6) how many triangles it holds: the triangle records
+                // are requested without waiting for the header, which is read once, after the tests, for the exit face.
+                const uint32_t off = MCPT_LEAF_OFF(leaf);
                 if (state == ST_INNER || (TRICAP && state == ST_LEAF)) {
-                    const float4 h0 = ldg4(p.sc.leaf_hdr + 4 * leaf), h1 = ldg4(p.sc.leaf_hdr + 4 * leaf + 1);
-                    if (!TRICAP || state == ST_INNER) { li = __float_as_uint(h0.w); lend = li + __float_as_uint(h1.w); }
-                    test_leaf(TRICAP ? min(lend, li + static_cast<uint32_t>(p.tri_cap)) : lend);
+                    if (!TRICAP || state == ST_INNER) {
+                        uint32_t cnt = MCPT_LEAF_CNT(leaf);
+                        if (cnt == 7u) cnt = __float_as_uint(ldg4(p.sc.leaf_blob + off + 1).w);
+                        li = off + 4u; lend = li + 3u * cnt;
+                    }
+                    test_leaf(TRICAP ? min(lend, li + 3u * static_cast<uint32_t>(p.tri_cap)) : lend);
                     if (TRICAP) state = li < lend ? ST_LEAF : ST_INNER;
                 }
                 if (state == ST_INNER) {
-                    const float4 h0 = ldg4(p.sc.leaf_hdr + 4 * leaf), h1 = ldg4(p.sc.leaf_hdr + 4 * leaf + 1);
-                    const LeafExit e = leaf_exit(p.sc, leaf, h0, h1, ox, oy, oz, ix, iy, iz, nearBits);
+                    const float4 h0 = ldg4(p.sc.leaf_blob + off), h1 = ldg4(p.sc.leaf_blob + off + 1);
+                    const LeafExit e = leaf_exit(p.sc, off, h0, h1, ox, oy, oz, ix, iy, iz, nearBits);
                     // No hop counter here (it costs a register the kernel does not have; intersect_ropes keeps one):
                     // the walk terminates structurally.  The face taken on each axis is fixed by the ray's sign bits,
                     // a rope's subtree lies wholly beyond that face, so the cell's bound on the exit axis moves

@@ -1,8 +1,11 @@
 // Random streams and BSDF direction samplers (device).
 //
 // Samplers follow rtx.hlsl:213-302 statement by statement (same special cases, same operand
-// order); this translation unit is compiled with -fmad=false and without fast-math so the only
-// differences from the CPU oracle are libm-vs-CUDA ulps in pow/sin/cos.
+// order); this translation unit is compiled with -fmad=false and without fast-math.  The differences
+// from the CPU oracle are a few ulps per direction: libm-vs-CUDA pow/sin/cos, and (MCPT_FAST_SHADE,
+// default) the hardware's approximate reciprocal square root / square root (MUFU.RSQ / MUFU.SQRT,
+// <= 2 ulp) and sincospif in place of the IEEE sequences -- HLSL's own rsqrt/sqrt/sincos carry no
+// tighter guarantee than that.  The intersection arithmetic (intersect.cuh) is not touched by this.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -21,7 +24,37 @@ __device__ __forceinline__ F3 operator*(F3 a, F3 b) { return {a.x * b.x, a.y * b
 __device__ __forceinline__ F3 operator/(F3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
 __device__ __forceinline__ F3 operator-(F3 a) { return {-a.x, -a.y, -a.z}; }
 __device__ __forceinline__ float dot(F3 a, F3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-__device__ __forceinline__ F3 normalize(F3 v) { return v * (1.0f / sqrtf(dot(v, v))); }
+#ifndef MCPT_FAST_SHADE
+#define MCPT_FAST_SHADE 1
+#endif
+// 1/sqrt(x) and sqrt(x) for shading directions: one MUFU instruction each instead of ~10-20 (IEEE sqrt + IEEE divide).
+__device__ __forceinline__ float shade_rsqrt(float x) {
+#if MCPT_FAST_SHADE
+    float y;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+#else
+    return 1.0f / sqrtf(x);
+#endif
+}
+__device__ __forceinline__ float shade_sqrt(float x) {
+#if MCPT_FAST_SHADE
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+#else
+    return sqrtf(x);
+#endif
+}
+// sin and cos of 2 pi y
+__device__ __forceinline__ void shade_sincos_2pi(float y, float* s, float* c) {
+#if MCPT_FAST_SHADE
+    sincospif(2.0f * y, s, c);
+#else
+    sincosf(2 * 3.14159265358979323846f * y, s, c);
+#endif
+}
+__device__ __forceinline__ F3 normalize(F3 v) { return v * shade_rsqrt(dot(v, v)); }
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based: key = (pixel, seed),
 // counter = (sample, slot, block, 0); slot 0 = camera jitter, slot b+1 = scattering event b,
@@ -128,10 +161,14 @@ __device__ __forceinline__ F3 sample_fresnel(RNG& rng, F3 normal, F3 dir, float 
 __device__ __forceinline__ F3 rotate_to(F3 d, F3 normal, bool divideByInvlen) {
     if (fabsf(normal.y + 1) < MCPT_EPS) return -d;
     if (fabsf(normal.y - 1) >= MCPT_EPS) {
-        const float invlen = 1.0f / sqrtf(1.0f - normal.y * normal.y);
+        const float invlen = shade_rsqrt(1.0f - normal.y * normal.y);
         F3 o;
         o.x = (normal.z * d.x + normal.x * normal.y * d.z) * invlen + normal.x * d.y;
+#if MCPT_FAST_SHADE
+        o.y = normal.y * d.y - d.z * ((1.0f - normal.y * normal.y) * invlen);  // 1 / invlen
+#else
         o.y = divideByInvlen ? (normal.y * d.y - d.z / invlen) : (normal.y * d.y - d.z * (1.0f / invlen));
+#endif
         o.z = (-normal.x * d.x + normal.z * normal.y * d.z) * invlen + normal.z * d.y;
         return o;
     }
@@ -144,10 +181,9 @@ __device__ __forceinline__ F3 sample_phong(RNG& rng, F3 normal, F3 dir, float Ns
     const float x = rng.next();
     const float y = rng.next();
     const float cosT = powf(x, 1.0f / (Ns + 1));
-    const float sinT = sqrtf(1 - cosT * cosT);
-    const float phi = 2 * MCPT_PI * y;
+    const float sinT = shade_sqrt(1 - cosT * cosT);
     float s, c;
-    sincosf(phi, &s, &c);
+    shade_sincos_2pi(y, &s, &c);
     const F3 halfdir = rotate_to(f3(sinT * c, cosT, sinT * s), normal, true);
     return dir - halfdir * dot(dir, halfdir) * 2;
 }
@@ -157,11 +193,10 @@ template <class RNG>
 __device__ __forceinline__ F3 sample_hemi(RNG& rng, F3 normal) {
     const float x = rng.next();
     const float y = rng.next();
-    const float sinT = sqrtf(x);
-    const float cosT = sqrtf(1 - x);
-    const float phi = 2 * MCPT_PI * y;
+    const float sinT = shade_sqrt(x);
+    const float cosT = shade_sqrt(1 - x);
     float s, c;
-    sincosf(phi, &s, &c);
+    shade_sincos_2pi(y, &s, &c);
     return rotate_to(f3(sinT * c, cosT, sinT * s), normal, false);
 }
 

@@ -51,7 +51,7 @@ int main(int argc, char** argv) {
     mix(tree.split_value.data(), tree.split_value.size() * 4); mix(tree.leaf_ids.data(), tree.leaf_ids.size() * 4);
     mix(tree.leaf_count.data(), tree.leaf_count.size() * 4);
     uint64_t hp = 1469598103934665603ull;
-    { uint64_t keep = h; h = hp; mix(packed.leaf_hdr.data(), packed.leaf_hdr.size() * 16); mix(packed.leaf_tris.data(), packed.leaf_tris.size() * 16); mix(packed.rope_nodes.data(), packed.rope_nodes.size() * 8); hp = h; h = keep; }
+    { uint64_t keep = h; h = hp; mix(packed.leaf_blob.data(), packed.leaf_blob.size() * 16); mix(packed.leaf_tris.data(), packed.leaf_tris.size() * 16); mix(packed.rope_nodes.data(), packed.rope_nodes.size() * 8); hp = h; h = keep; }
     size_t hist[10] = {0};
     for (size_t k = 0; k < tree.num_nodes(); ++k)
         if (tree.split_axis[k] == 0) ++hist[std::min<uint32_t>(tree.leaf_count[k], 9u)];
