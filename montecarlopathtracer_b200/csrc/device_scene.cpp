@@ -160,6 +160,8 @@ DCamera make_camera(const float eye[3], const float at[3], const float up[3], fl
     float aspect = 1.0f * width / height;
     cam.p22 = static_cast<float>(1.0 / std::tan(static_cast<double>(fovy) * 0.5));
     cam.p11 = cam.p22 / aspect;
+    cam.sx = static_cast<float>(2.0 / (static_cast<double>(width) * cam.p11));
+    cam.sy = static_cast<float>(2.0 / (static_cast<double>(height) * cam.p22));
     cam.tan_half = tanf(fovy * 0.5f);  // tan(projFOV * PW_PI / 360), CUTracer.cu:202
     cam.twin = twin;
     return cam;

@@ -53,6 +53,7 @@ struct DScene {
 struct DCamera {
     float inv[4][3];
     float p11, p22;
+    float sx, sy;    // 2 / (width p11), 2 / (height p22): the render kernels' one-product form of rtx.hlsl:391-392
     float tan_half;  // CUDA-twin camera: tan(hfov / 2)
     int twin;        // 0: rtx.hlsl camera, 1: CUTracer.cu:189-212
 };

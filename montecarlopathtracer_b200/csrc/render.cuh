@@ -34,7 +34,10 @@ struct RenderParams {
     unsigned long long* ray_counter;
 };
 
-// rtx.hlsl:384-398
+// rtx.hlsl:384-398.  EXACT: the shader's expressions with IEEE divides and square root (primary_rays_kernel: rays
+// bit-equal to the oracle's).  The render kernels (MCPT_FAST_SHADE) use the same map with the two quotients per
+// coordinate folded into one host-computed factor and the hardware rsqrt: a few ulps in the ray, ~45 instructions less.
+template <bool EXACT = true>
 __device__ __forceinline__ void camera_ray(const DCamera& cam, int width, int height, uint32_t px, uint32_t py,
                                            float u1, float u2, F3& org, F3& dir) {
     if (cam.twin) {
@@ -55,8 +58,14 @@ __device__ __forceinline__ void camera_ray(const DCamera& cam, int width, int he
     }
     const float biasx = static_cast<float>(px) + (u1 - 0.5f);
     const float biasy = static_cast<float>(py) + (u2 - 0.5f);
-    const float d0 = (2.0f * biasx / static_cast<float>(width) - 1) / cam.p11;
-    const float d1 = (1 - 2.0f * biasy / static_cast<float>(height)) / cam.p22;
+    float d0, d1;
+    if (EXACT) {
+        d0 = (2.0f * biasx / static_cast<float>(width) - 1) / cam.p11;
+        d1 = (1 - 2.0f * biasy / static_cast<float>(height)) / cam.p22;
+    } else {
+        d0 = (biasx - 0.5f * static_cast<float>(width)) * cam.sx;
+        d1 = (0.5f * static_cast<float>(height) - biasy) * cam.sy;
+    }
     const float d2 = -1.0f;
     float w[3], f[3];
 #pragma unroll
@@ -65,7 +74,8 @@ __device__ __forceinline__ void camera_ray(const DCamera& cam, int width, int he
         f[i] = w[i] + cam.inv[3][i];
     }
     org = f3(f[0], f[1], f[2]);
-    const float inv = 1.0f / sqrtf(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+    const float len2 = w[0] * w[0] + w[1] * w[1] + w[2] * w[2];
+    const float inv = EXACT ? 1.0f / sqrtf(len2) : shade_rsqrt(len2);
     dir = f3(w[0] * inv, w[1] * inv, w[2] * inv);
 }
 
@@ -109,7 +119,7 @@ __global__ void __launch_bounds__(256) render_kernel(const RenderParams p) {
         rng.start(pixel, p.seed, static_cast<uint32_t>(p.sample_begin + s), p.frame_seeds ? p.frame_seeds[s] : 0u);
         float u1 = 0.5f, u2 = 0.5f;
         if (p.jitter) { u1 = rng.next(); u2 = rng.next(); }
-        camera_ray(p.cam, p.width, p.height, px, py, u1, u2, org, dir);
+        camera_ray<!MCPT_FAST_SHADE>(p.cam, p.width, p.height, px, py, u1, u2, org, dir);
         thr = f3(1, 1, 1); cur = f3(0, 0, 0);
         bounce = 0; lastWasNee = false;
     };

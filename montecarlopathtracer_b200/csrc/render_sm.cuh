@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         float u1 = 0.5f, u2 = 0.5f;
         if (p.jitter) { u1 = rng.next(); u2 = rng.next(); }
         F3 o, d;
-        camera_ray(p.cam, p.width, p.height, px, py, u1, u2, o, d);
+        camera_ray<!MCPT_FAST_SHADE>(p.cam, p.width, p.height, px, py, u1, u2, o, d);
         ox = o.x; oy = o.y; oz = o.z; dx = d.x; dy = d.y; dz = d.z;
         thr = f3(1, 1, 1); cur = f3(0, 0, 0);
         bounce = 0; lastWasNee = false; shadow = false;
@@ -134,7 +134,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
             float u1 = 0.5f, u2 = 0.5f;
             if (p.jitter) { u1 = r.next(); u2 = r.next(); }
             F3 o, d;
-            camera_ray(p.cam, p.width, p.height, px, py, u1, u2, o, d);
+            camera_ray<!MCPT_FAST_SHADE>(p.cam, p.width, p.height, px, py, u1, u2, o, d);
             float* q = camq + threadIdx.x;
             q[0] = o.x; q[BLOCK] = o.y; q[2 * BLOCK] = o.z; q[3 * BLOCK] = d.x; q[4 * BLOCK] = d.y; q[5 * BLOCK] = d.z;
             q[6 * BLOCK] = __uint_as_float(r.save());

@@ -136,6 +136,30 @@ __device__ __forceinline__ F3 sample_fresnel(RNG& rng, F3 normal, F3 dir, float 
     const float x = rng.next();
     F3 outdir;
     const float ndoti = dot(dir, normal);
+#if MCPT_FAST_SHADE
+    // pow(c, 5) by three products; the quotients by Ni as products with one reciprocal (each within an ulp or two of
+    // the IEEE sequence below, which costs ~50 + 5 x 10 instructions)
+    const float c1 = 1 - fabsf(ndoti), c2 = c1 * c1;
+    Tr = Tr * (1 - c2 * c2 * c1);
+    if (x < Tr) {
+        float rNi;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rNi) : "f"(Ni));
+        if (ndoti <= 0) {
+            const float alpha = -ndoti * rNi - shade_sqrt(1 - (1 - ndoti * ndoti) * rNi * rNi);
+            outdir = normal * alpha + dir * rNi;
+        } else {
+            const float test = 1 - (1 - ndoti * ndoti) * Ni * Ni;
+            if (test < 0) {
+                outdir = dir - normal * ndoti * 2;
+            } else {
+                const float alpha = -ndoti * Ni + shade_sqrt(test);
+                outdir = normal * alpha + dir * Ni;
+            }
+        }
+    } else {
+        outdir = dir - normal * ndoti * 2;
+    }
+#else
     Tr = Tr * (1 - powf(1 - fabsf(ndoti), 5.0f));
     if (x < Tr) {
         if (ndoti <= 0) {
@@ -153,6 +177,7 @@ __device__ __forceinline__ F3 sample_fresnel(RNG& rng, F3 normal, F3 dir, float 
     } else {
         outdir = dir - normal * dot(dir, normal) * 2;
     }
+#endif
     return normalize(outdir);
 }
 
@@ -180,8 +205,16 @@ template <class RNG>
 __device__ __forceinline__ F3 sample_phong(RNG& rng, F3 normal, F3 dir, float Ns) {
     const float x = rng.next();
     const float y = rng.next();
+#if MCPT_FAST_SHADE
+    // x^(1/(Ns+1)) = 2^(log2(x) / (Ns+1)): x in (0,1], the exponent in (0, 1/2): MUFU.LG2's absolute error (2^-22) is
+    // scaled down by it, the result is within ~1 ulp of powf's
+    float rN;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rN) : "f"(Ns + 1));
+    const float cosT = exp2f(__log2f(x) * rN);
+#else
     const float cosT = powf(x, 1.0f / (Ns + 1));
-    const float sinT = shade_sqrt(1 - cosT * cosT);
+#endif
+    const float sinT = shade_sqrt(fmaxf(1 - cosT * cosT, 0.0f));
     float s, c;
     shade_sincos_2pi(y, &s, &c);
     const F3 halfdir = rotate_to(f3(sinT * c, cosT, sinT * s), normal, true);
