@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                         done = true;  // :313-316
                     } else if (bounce >= p.depth) {
                         const float illum = fmaxf(fmaxf(thr.x, thr.y), thr.z);  // :317-328
-                        if (illum > rng.next()) thr = thr / illum; else done = true;
+                        if (illum > rng.next()) thr = MCPT_FAST_SHADE ? thr * shade_rcp(illum) : thr / illum; else done = true;
                     }
                     if (!done) {
                         const float4 s0 = ldg4(p.sc.tri_shade + 3 * htri);
@@ -278,20 +278,20 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                                     while (e + 1 < p.sc.num_emitters && u0 > ldg4(p.sc.emitters + 3 * e + 1).w) ++e;
                                     const float4 ea = ldg4(p.sc.emitters + 3 * e), eu = ldg4(p.sc.emitters + 3 * e + 1),
                                                  ev = ldg4(p.sc.emitters + 3 * e + 2);
-                                    const float su = sqrtf(ub);
+                                    const float su = shade_sqrt(ub);
                                     const float b1 = 1.0f - su, b2 = uc * su;
                                     const F3 y = f3(ea.x + b1 * eu.x + b2 * ev.x, ea.y + b1 * eu.y + b2 * ev.y, ea.z + b1 * eu.z + b2 * ev.z);
                                     F3 w = y - hp;
                                     const float r2 = dot(w, w);
-                                    w = w * (1.0f / sqrtf(r2));
+                                    w = w * shade_rsqrt(r2);
                                     const F3 ng = f3(eu.y * ev.z - eu.z * ev.y, eu.z * ev.x - eu.x * ev.z, eu.x * ev.y - eu.y * ev.x);
-                                    const float cosy = fabsf(dot(ng, w)) / (2.0f * ea.w);
+                                    const float cosy = fabsf(dot(ng, w)) * shade_rcp(2.0f * ea.w);
                                     const float cosx = dot(flip ? -normal : normal, w);
                                     if (cosx > 0 && cosy > 0 && r2 > 0) {
                                         shTri = __float_as_uint(ev.w);
                                         const uint32_t lmat = __float_as_uint(ldg4(p.sc.tri_shade + 3 * shTri).w);
                                         const float4 lKa = ldg4(p.sc.mats + 3 * lmat);
-                                        const float g = cosx * cosy * p.sc.emitter_area / (MCPT_PI * r2);
+                                        const float g = cosx * cosy * p.sc.emitter_area * shade_rcp(MCPT_PI * r2);
                                         shVal = thr * f3(lKa.x, lKa.y, lKa.z) * (g * p.emission_scale);
                                         shadow = true;
                                         ++nrays;

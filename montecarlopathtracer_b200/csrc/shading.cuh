@@ -54,6 +54,15 @@ __device__ __forceinline__ void shade_sincos_2pi(float y, float* s, float* c) {
     sincosf(2 * 3.14159265358979323846f * y, s, c);
 #endif
 }
+__device__ __forceinline__ float shade_rcp(float x) {
+#if MCPT_FAST_SHADE
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+#else
+    return 1.0f / x;
+#endif
+}
 __device__ __forceinline__ F3 normalize(F3 v) { return v * shade_rsqrt(dot(v, v)); }
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based: key = (pixel, seed),
