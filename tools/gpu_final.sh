@@ -11,6 +11,6 @@ python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/plain.log 2>
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1
 python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:render_kernel_sm -s 1 -c 1 -f -o gpurun_out/prof_final3_K2 \
+ncu --set full --clock-control none --import-source on -k regex:render_kernel_sm -s 1 -c 1 -f -o gpurun_out/prof_final_K2 \
     python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
 ls -la gpurun_out | head -40
