@@ -97,7 +97,7 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.state_machine = (cfg->flags & MCPT_FLAG_SIMPLE_KERNEL) == 0;
     r.shade_threshold = env_int("MCPT_SM_SHADE", 18);      // tuning knobs, defaults from profiles/r1_tuning.md
     r.min_blocks = env_int("MCPT_SM_MINBLOCKS", 4);
-    r.variant = env_int("MCPT_SM_VARIANT", 119);
+    r.variant = env_int("MCPT_SM_VARIANT", 503);
     r.cam_threshold = env_int("MCPT_SM_CAMR", 16);
     r.tri_cap = std::max(1, env_int("MCPT_SM_TRICAP", 4));
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {

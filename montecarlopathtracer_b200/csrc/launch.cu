@@ -10,7 +10,7 @@
 
 // Shipping configuration of the persistent-lane kernel (profiles/r1_tuning.md).
 #ifndef MCPT_SM_VARIANT
-#define MCPT_SM_VARIANT 119
+#define MCPT_SM_VARIANT 503
 #endif
 #ifndef MCPT_SM_MIN_BLOCKS
 #define MCPT_SM_MIN_BLOCKS 4
@@ -164,7 +164,7 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
             return cudaGetLastError();
         }
         switch (r.variant) {
-            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20) MCPT_V(55) MCPT_V(53) MCPT_V(119)
+            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20) MCPT_V(55) MCPT_V(53) MCPT_V(119) MCPT_V(247) MCPT_V(375) MCPT_V(503)
             default: return cudaErrorInvalidValue;
         }
 #undef MCPT_V

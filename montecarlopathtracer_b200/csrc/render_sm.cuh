@@ -30,10 +30,15 @@ enum : uint32_t { ST_INNER = 0u, ST_LEAF = 1u, ST_SHADE = 2u, ST_DEAD = 3u };
 //   bit 5  div3_rn: the three IEEE quotients of a surviving triangle share one reciprocal and one range guard;
 //   bit 6  (with bit 1) at most `tri_cap` triangle tests per lane and round: a lane in a bigger leaf stays in it
 //          (ST_LEAF) and goes on next round, so the round's triangle loop is not as long as the warp's biggest leaf.
+//   bit 7  (with bit 1) a bounce or shadow ray starts its walk in the leaf of the hit it leaves, 0.01 BEHIND its origin
+//          (the hit point lies in that leaf's cell): no clip against the scene box, no containment test of the hint, no
+//          point location from the root when the 0.01 offset has left the cell -- the walk crosses those cells itself;
+//   bit 8  tri_test<.., LEAN>: inside div3_guard's range the `> 0` comparisons of the three quotients are implied.
 template <class RNG, bool NEE, bool MOMENTS, int MIN_BLOCKS, int VAR, int BLOCK = 256>
 __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const RenderParams p, const int shadeThreshold) {
     constexpr bool LEAFREC = (VAR & 1) != 0, ROPES = (VAR & 2) != 0, FASTREJ = (VAR & 4) != 0, STATS = (VAR & 8) != 0, CAMQ = (VAR & 16) != 0,
-                   DIV3 = (VAR & 32) != 0, TRICAP = ROPES && (VAR & 64) != 0;
+                   DIV3 = (VAR & 32) != 0, TRICAP = ROPES && (VAR & 64) != 0, STARTHINT = ROPES && (VAR & 128) != 0,
+                   LEAN = (VAR & 256) != 0;
     __shared__ float camq[CAMQ ? 7 * BLOCK : 1];  // CAMQ: parked primary ray {o, d, rng state} per thread
     bool camReady = false;
     uint32_t st[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
@@ -77,6 +82,14 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
             ix = __frcp_rn(dx); iy = __frcp_rn(dy); iz = __frcp_rn(dz);
         }
         nearBits = (ix < 0.0f ? 1u : 0u) | (iy < 0.0f ? 2u : 0u) | (iz < 0.0f ? 4u : 0u);
+        if (STARTHINT && !(bounce == 0u && !shadow) && hintLeaf != 0xFFFFFFFFu) {
+            // The ray leaves a hit at o - 0.01 d, inside the cell of `hintLeaf` (the walk that found the hit stopped there).
+            // Starting the walk at that point costs a leaf visit or two when the offset has left the cell; triangles
+            // behind the origin fail `t > 0` as they do in the origin's own leaf.
+            best = 10000.0f; htri = 0xFFFFFFFFu; hbeta = 0; hgamma = 0;
+            leaf = hintLeaf; tmin = -0.0101f; state = ST_INNER;
+            return;
+        }
         tmin = 0.0f; tmax = 10000.0f;
         float tn = (p.sc.bmin[0] - ox) * ix, tf = (p.sc.bmax[0] - ox) * ix;
         if (ix < 0.0f) { const float sw = tn; tn = tf; tf = sw; }
@@ -195,7 +208,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
             if (STATS) ++myTris;
             if (ROPES) {
                 // li walks the leaf's block in float4 units; results written in place, inside the test's (rare) accept branch
-                tri_test<FASTREJ, DIV3>(p.sc.leaf_blob + li, ox, oy, oz, dx, dy, dz, best, best, hbeta, hgamma, &htri);
+                tri_test<FASTREJ, DIV3, LEAN>(p.sc.leaf_blob + li, ox, oy, oz, dx, dy, dz, best, best, hbeta, hgamma, &htri);
             } else if (LEAFREC) {
                 tri_test<FASTREJ, DIV3>(p.sc.leaf_tris + 3 * li, ox, oy, oz, dx, dy, dz, best, best, hbeta, hgamma, &htri);
             } else {
