@@ -325,20 +325,20 @@ def main():
     line["roofline"] = {"bound": "hbm", "achieved": abytes / t_launch / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": abytes / t_launch / 1e9 / hbm_peak,
                         # dram__bytes_read.sum + dram__bytes_write.sum of ONE render_kernel_sm launch at the K2 size
-                        # (profiles/r1h_ncu_full_render_kernel_sm_K2_raw.csv; the four 16 MB accumulation slices mostly stay in L2); other workloads were not captured
-                        "traffic": 24098816 if (args.workload == "K2" and not args.spp) else None,
+                        # (profiles/r1i_ncu_full_render_kernel_sm_K2_raw.csv; the four 16 MB accumulation slices mostly stay in L2); other workloads were not captured
+                        "traffic": 23419904 if (args.workload == "K2" and not args.spp) else None,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                         "kernel": "render_kernel_sm", "launch_ms": t_launch * 1e3,
                         "algorithmic_bytes_per_ray": nn * B_NODE + nt * B_TRI, "algorithmic_flops_per_ray": nn * F_NODE + nt * F_TRI,
                         "fp32": {"achieved_gflops": aflops / t_launch / 1e9, "peak_gflops": fp32_peak, "frac": aflops / t_launch / 1e9 / fp32_peak},
                         # The resource that actually binds: warp-instruction issue slots (148 SMs x 4 schedulers x 1 per
                         # clock).  warp instructions per ray and threads per instruction are constants of the committed
-                        # ncu capture (profiles/r1h_*: smsp__inst_executed.sum / rays, thread_inst / inst), K2 only.
-                        "issue": ({"warp_inst_per_ray": 86.1, "threads_per_inst": 11.52,
-                                   "achieved_ginst_s": 86.1 * rays_per_launch / t_launch / 1e9,
+                        # ncu capture (profiles/r1i_*: smsp__inst_executed.sum / rays, thread_inst / inst), K2 only.
+                        "issue": ({"warp_inst_per_ray": 82.9, "threads_per_inst": 11.37,
+                                   "achieved_ginst_s": 82.9 * rays_per_launch / t_launch / 1e9,
                                    "peak_ginst_s": 148 * 4 * ((clocks or {}).get("sm_mhz") or 1965.0) / 1e3,
-                                   "frac": 86.1 * rays_per_launch / t_launch / 1e9 / (148 * 4 * ((clocks or {}).get("sm_mhz") or 1965.0) / 1e3),
-                                   "source": "profiles/r1h_ncu_full_render_kernel_sm_K2_raw.csv"}
+                                   "frac": 82.9 * rays_per_launch / t_launch / 1e9 / (148 * 4 * ((clocks or {}).get("sm_mhz") or 1965.0) / 1e3),
+                                   "source": "profiles/r1i_ncu_full_render_kernel_sm_K2_raw.csv"}
                                   if (args.workload == "K2" and not args.spp) else None),
                         "note": "node/triangle fetches are served by L1/L2 (scene < 1 MB); HBM traffic is only the accumulation buffer. "
                                 "The binding limit is FP32/issue rate x SIMT efficiency, see profiles/."}
