@@ -33,7 +33,8 @@ enum {
     MCPT_ERR_IO = 2,        /* file missing or malformed                */
     MCPT_ERR_CUDA = 3,      /* CUDA runtime error (text in last_error)  */
     MCPT_ERR_NO_DEVICE = 4, /* no usable GPU: the product has no CPU path */
-    MCPT_ERR_NCCL = 5
+    MCPT_ERR_NCCL = 5,
+    MCPT_ERR_INTERNAL = 6   /* a self-check of the library's own tables failed */
 };
 
 /* KD-tree construction rule. */
@@ -133,6 +134,10 @@ int mcpt_load_obj(const char* obj_path, const char* mtl_base, int loader, int bu
 /* Same from a baked scene container (scenes/ *.mcpt, magic "MCPTSCN1"). */
 int mcpt_load_scene_file(const char* path, int build_mode);
 int mcpt_get_tree_info(mcpt_tree_info* info);
+/* Host-side structural check of the stackless-traversal tables built for the current geometry (leaf blocks, leaf
+ * handles, neighbour links: csrc/kd_ropes.cpp check_ropes); needs no device.  MCPT_OK, or MCPT_ERR_INTERNAL with the
+ * first inconsistency in mcpt_last_error(). */
+int mcpt_check_stackless_layout(void);
 /* Copies the built tree out in the reference's BFS layout (ShaderResource.hpp:128-179);
  * any pointer may be NULL. aabb6: 6 floats per node. */
 int mcpt_get_tree(uint32_t* left, uint32_t* right, float* aabb6, uint32_t* split_axis,

@@ -176,6 +176,15 @@ int mcpt_destroy_geometry(void) {
     return MCPT_OK;
 }
 
+int mcpt_check_stackless_layout(void) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
+    std::string err;
+    if (!check_ropes(c.tree, c.packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
+    return MCPT_OK;
+}
+
 int mcpt_get_tree_info(mcpt_tree_info* info) {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);

@@ -21,7 +21,10 @@
 //               A rope is 0xFFFFFFFF = outside the scene; bit 31 set = the neighbour is one leaf: its handle in the
 //               low bits, no node to load; else a node index.
 //   rope_nodes  uint2 per node: inner = kd_nodes entry; leaf = {leaf handle, (count << 2) | 3}
+#include <algorithm>
 #include <cstring>
+#include <string>
+#include <utility>
 
 #include "device_scene.h"
 
@@ -119,6 +122,87 @@ bool build_ropes(const HostTree& tree, PackedScene& out) {
     for (int i = 0; i < 3; ++i) { root.lo[i] = tree.aabb[i]; root.hi[i] = tree.aabb[3 + i]; }
     const uint32_t none[6] = {kNone, kNone, kNone, kNone, kNone, kNone};
     b.walk(0u, root, none);
+    return true;
+}
+
+// Structural check of what build_ropes produced (host only; mcpt_check_stackless_layout, CPU tests):
+//   * the blocks follow each other in leaf order, every handle carries its block's offset and min(count, 7), the
+//     header repeats the tree's first/count and the records are the leaf_tris records of that leaf;
+//   * for every leaf and face: a missing rope only where the face lies on the scene box; otherwise the rope's cell touches the face
+//     from the other side and covers it in the two other axes (so the cell behind any exit point is below the rope),
+//     a leaf rope names a real leaf, and a node rope is the deepest possible (its plane cuts the face).
+// Cells are recomputed from the split planes, independently of Builder::walk's bookkeeping.
+bool check_ropes(const HostTree& t, const PackedScene& out, std::string& err) {
+    const size_t nN = t.num_nodes();
+    std::vector<Cell> cell(nN);
+    for (int i = 0; i < 3; ++i) { cell[0].lo[i] = t.aabb[i]; cell[0].hi[i] = t.aabb[3 + i]; }
+    for (size_t k = 0; k < nN; ++k) {  // BFS order: a parent comes before its children
+        if (t.split_axis[k] == 0) continue;
+        const int a = static_cast<int>(t.split_axis[k]) - 1;
+        const uint32_t L = t.left[k];
+        if (L + 1 >= nN) { err = "child index out of range"; return false; }
+        cell[L] = cell[k]; cell[L + 1] = cell[k];
+        cell[L].hi[a] = t.split_value[k];
+        cell[L + 1].lo[a] = t.split_value[k];
+    }
+    std::vector<std::pair<uint32_t, uint32_t>> byOrdinal;  // (ordinal, node)
+    for (size_t k = 0; k < nN; ++k)
+        if (t.split_axis[k] == 0) byOrdinal.emplace_back(out.leaf_order[k], static_cast<uint32_t>(k));
+    std::sort(byOrdinal.begin(), byOrdinal.end());
+    if (out.rope_nodes.size() != nN) { err = "rope_nodes size"; return false; }
+    std::vector<uint32_t> nodeOfOffset;  // block offset -> leaf node (sparse)
+    size_t units = 0;
+    auto bits = [](float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; };
+    for (const auto& on : byOrdinal) {
+        const uint32_t k = on.second, count = t.leaf_count[k], h = out.rope_nodes[k].x;
+        if ((h & kLeafOffsetMask) != units || ((h >> 28) & 7u) != (count < 7u ? count : 7u) || (h & kRopeIsLeaf)) { err = "leaf handle of node " + std::to_string(k); return false; }
+        if (units + 4 + 3 * static_cast<size_t>(count) > out.leaf_blob.size()) { err = "leaf block past the end"; return false; }
+        const float4* blk = out.leaf_blob.data() + units;
+        if (bits(blk[0].w) != out.kd_nodes[k].x || bits(blk[1].w) != count) { err = "leaf header first/count of node " + std::to_string(k); return false; }
+        for (int i = 0; i < 3; ++i) {
+            const float lo = i == 0 ? blk[0].x : (i == 1 ? blk[0].y : blk[0].z), hi = i == 0 ? blk[1].x : (i == 1 ? blk[1].y : blk[1].z);
+            if (lo != cell[k].lo[i] || hi != cell[k].hi[i]) { err = "leaf cell of node " + std::to_string(k); return false; }
+        }
+        if (std::memcmp(blk + 4, out.leaf_tris.data() + 3 * static_cast<size_t>(out.kd_nodes[k].x), 48 * static_cast<size_t>(count)) != 0) { err = "leaf records of node " + std::to_string(k); return false; }
+        if (nodeOfOffset.size() <= units) nodeOfOffset.resize(units + 1, kNone);
+        nodeOfOffset[units] = k;
+        units += 4 + 3 * static_cast<size_t>(count);
+    }
+    if (out.leaf_blob.size() != units + 3) { err = "leaf_blob size"; return false; }
+    for (const auto& on : byOrdinal) {
+        const uint32_t k = on.second;
+        const Cell& c = cell[k];
+        const float4* blk = out.leaf_blob.data() + (out.rope_nodes[k].x & kLeafOffsetMask);
+        const uint32_t rope[6] = {bits(blk[2].x), bits(blk[2].y), bits(blk[2].z), bits(blk[2].w), bits(blk[3].x), bits(blk[3].y)};
+        for (int f = 0; f < 6; ++f) {
+            const int a = f >> 1;
+            const bool maxSide = (f & 1) != 0;
+            const std::string where = "rope " + std::to_string(f) + " of node " + std::to_string(k);
+            const bool onBox = maxSide ? c.hi[a] == cell[0].hi[a] : c.lo[a] == cell[0].lo[a];
+            if (rope[f] == kNone) {
+                if (!onBox) { err = where + ": missing"; return false; }
+                continue;
+            }
+            // (a face ON the scene box can still have a neighbour: a split plane that coincides with the box leaves a flat cell)
+            uint32_t target;
+            if (rope[f] & kRopeIsLeaf) {
+                const uint32_t off = rope[f] & kLeafOffsetMask;
+                if (off >= nodeOfOffset.size() || nodeOfOffset[off] == kNone) { err = where + ": not a leaf handle"; return false; }
+                target = nodeOfOffset[off];
+                if (out.rope_nodes[target].x != (rope[f] & ~kRopeIsLeaf)) { err = where + ": handle bits"; return false; }
+            } else {
+                target = rope[f];
+                if (target >= nN || t.split_axis[target] == 0) { err = where + ": not an inner node"; return false; }
+                const int sa = static_cast<int>(t.split_axis[target]) - 1;
+                const float sv = t.split_value[target];
+                if (sa == a || !(sv > c.lo[sa] && sv < c.hi[sa])) { err = where + ": not the deepest covering node"; return false; }
+            }
+            const Cell& n = cell[target];
+            if (maxSide ? n.lo[a] != c.hi[a] : n.hi[a] != c.lo[a]) { err = where + ": target does not touch the face"; return false; }
+            for (int b = 0; b < 3; ++b)
+                if (b != a && !(n.lo[b] <= c.lo[b] && n.hi[b] >= c.hi[b])) { err = where + ": target does not cover the face"; return false; }
+        }
+    }
     return true;
 }
 

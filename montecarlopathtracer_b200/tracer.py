@@ -25,6 +25,7 @@ FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL, FLAG_SIMPLE_KERNEL =
 ISECT_REFERENCE, ISECT_KD, ISECT_ROPES = 0, 1, 2
 TRACER_MCRT, TRACER_CUDA_TWIN = 0, 1
 ERR_NO_DEVICE = 4
+ERR_INTERNAL = 6
 
 _vp = C.c_void_p
 
@@ -76,6 +77,7 @@ def lib() -> C.CDLL:
     L.mcpt_load_obj.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
     L.mcpt_load_scene_file.argtypes = [C.c_char_p, C.c_int]
     L.mcpt_get_tree_info.argtypes = [C.POINTER(TreeInfo)]
+    L.mcpt_check_stackless_layout.argtypes = []
     L.mcpt_get_tree.argtypes = [_vp] * 8
     L.mcpt_get_scene.argtypes = [_vp] * 5
     L.mcpt_default_render_cfg.argtypes = [C.POINTER(RenderCfg), C.c_int, C.c_int, C.c_int, C.c_int]
@@ -142,6 +144,11 @@ def load_scene_file(path: str, build_mode: int = BUILD_REFERENCE) -> None:
 
 def destroy_geometry() -> None:
     _check(lib().mcpt_destroy_geometry())
+
+
+def check_stackless_layout() -> None:
+    """Host-side structural check of the leaf blocks and neighbour links built for the current geometry (no device)."""
+    _check(lib().mcpt_check_stackless_layout())
 
 
 def tree_info() -> TreeInfo:

@@ -63,6 +63,26 @@ def test_host_builder_on_tessellated_surface(tracer, oracle):
     tracer.destroy_geometry()
 
 
+@pytest.mark.parametrize("build_mode", [0, 1], ids=["reference_rule", "sah"])
+@pytest.mark.parametrize("name", ["scene01", "scene01_lambert", "scene02", "scene03", "heightfield"])
+def test_stackless_layout_is_consistent(tracer, scenes, name, build_mode):
+    """Leaf blocks, leaf handles and neighbour links of the render path's tables (csrc/kd_ropes.cpp), checked on the host for
+    both builders: blocks contiguous in leaf order, handles = (offset, min(count, 7)), records = the leaf's triangle records,
+    and every rope touches and covers the face it belongs to (or the face lies on the scene box)."""
+    if name == "heightfield":
+        from montecarlopathtracer_b200 import scenes as gen
+        s0 = scenes["scene01_lambert"]
+        v, n, t, m = gen.cornell_heightfield((s0.verts, s0.normals, s0.tris, s0.mats), 60)
+    else:
+        s = scenes[name]
+        v, n, t, m = s.verts, s.normals, s.tris, s.mats
+    tracer.create_geometry(v, n, t, m, build_mode)
+    tracer.check_stackless_layout()
+    tracer.destroy_geometry()
+    with pytest.raises(tracer.McptError):
+        tracer.check_stackless_layout()  # no geometry
+
+
 def test_scene_file_round_trip(tracer, scenes, tmp_path):
     p = str(tmp_path / "s.mcpt")
     scenes["scene02"].save(p)
