@@ -348,6 +348,7 @@ void build_sah_tree(const HostScene& scene, HostTree& out) {
             ++out.num_leaves;
         }
     }
+    if (std::getenv("MCPT_BUILD_TIMING")) std::fprintf(stderr, "sah: recursion + flatten %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
     out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 
