@@ -326,26 +326,32 @@ void build_sah_tree(const HostScene& scene, HostTree& out) {
     const size_t nN = order.size();
     out.left.resize(nN); out.aabb.resize(6 * nN); out.split_axis.resize(nN); out.split_value.resize(nN);
     out.leaf_offset.resize(nN); out.leaf_count.resize(nN);
-    // children of node k are the next two unassigned BFS slots: recompute positions
-    size_t next = 1;
+    // children of node k are the next two unassigned BFS slots; a leaf's ids start where the previous leaves' end:
+    // two running sums (serial, cheap), then every node is filled independently
+    {
+        size_t next = 1, idsSoFar = 0;
+        for (size_t k = 0; k < nN; ++k) {
+            const Node& n = nodes[static_cast<size_t>(order[k])];
+            out.leaf_offset[k] = static_cast<uint32_t>(idsSoFar);
+            if (n.axis >= 0) { out.left[k] = static_cast<uint32_t>(next); next += 2; }
+            else { out.left[k] = 0xFFFFFFFFu; idsSoFar += n.ids.size(); ++out.num_leaves; }
+            out.max_depth = std::max(out.max_depth, depthOf[k]);
+        }
+        out.leaf_ids.resize(idsSoFar);
+    }
+#pragma omp parallel for schedule(static) if (nN > 65536)
     for (size_t k = 0; k < nN; ++k) {
         const Node& n = nodes[static_cast<size_t>(order[k])];
         for (int i = 0; i < 3; ++i) { out.aabb[6 * k + i] = n.cell.lo[i]; out.aabb[6 * k + 3 + i] = n.cell.hi[i]; }
-        out.leaf_offset[k] = static_cast<uint32_t>(out.leaf_ids.size());
-        out.max_depth = std::max(out.max_depth, depthOf[k]);
         if (n.axis >= 0) {
-            out.left[k] = static_cast<uint32_t>(next);
-            next += 2;
             out.split_axis[k] = static_cast<uint32_t>(n.axis + 1);
             out.split_value[k] = n.plane;
             out.leaf_count[k] = 0;
         } else {
-            out.left[k] = 0xFFFFFFFFu;
             out.split_axis[k] = 0;
             out.split_value[k] = 0.0f;
             out.leaf_count[k] = static_cast<uint32_t>(n.ids.size());
-            out.leaf_ids.insert(out.leaf_ids.end(), n.ids.begin(), n.ids.end());
-            ++out.num_leaves;
+            std::copy(n.ids.begin(), n.ids.end(), out.leaf_ids.begin() + out.leaf_offset[k]);
         }
     }
     if (std::getenv("MCPT_BUILD_TIMING")) std::fprintf(stderr, "sah: recursion + flatten %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());

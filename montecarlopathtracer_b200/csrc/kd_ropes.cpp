@@ -60,7 +60,7 @@ struct Builder {
         return r;
     }
 
-    void walk(uint32_t node, const Cell& cell, const uint32_t ropes[6]) {
+    void walk(uint32_t node, const Cell& cell, const uint32_t ropes[6], int depth = 0) {
         if (t.split_axis[node] == 0) {
             float4* blk = out.leaf_blob.data() + (leafHandle[node] & kLeafOffsetMask);
             const uint32_t first = out.kd_nodes[node].x, count = t.leaf_count[node];
@@ -90,8 +90,16 @@ struct Builder {
             rl[f] = tighten(rl[f], f >> 1, (f & 1) != 0, cl);
             rr[f] = tighten(rr[f], f >> 1, (f & 1) != 0, cr);
         }
-        walk(L, cl, rl);
-        walk(R, cr, rr);
+        // subtrees write disjoint leaf blocks: the upper levels fan out as tasks (build_ropes opens the parallel region)
+        if (depth < 7) {
+#pragma omp task firstprivate(L, cl, rl, depth)
+            walk(L, cl, rl, depth + 1);
+            walk(R, cr, rr, depth + 1);
+#pragma omp taskwait
+        } else {
+            walk(L, cl, rl, depth + 1);
+            walk(R, cr, rr, depth + 1);
+        }
     }
 };
 
@@ -121,6 +129,8 @@ bool build_ropes(const HostTree& tree, PackedScene& out) {
     Cell root;
     for (int i = 0; i < 3; ++i) { root.lo[i] = tree.aabb[i]; root.hi[i] = tree.aabb[3 + i]; }
     const uint32_t none[6] = {kNone, kNone, kNone, kNone, kNone, kNone};
+#pragma omp parallel
+#pragma omp single
     b.walk(0u, root, none);
     return true;
 }
