@@ -69,6 +69,9 @@ bool clipped_bounds(const HostScene& s, uint32_t id, const Box& cell, Box& out) 
         for (int side = 0; side < 2 && n > 0; ++side) {
             const double plane = side == 0 ? cell.lo[axis] : cell.hi[axis];
             const double sign = side == 0 ? 1.0 : -1.0;  // keep sign * (x - plane) >= 0
+            bool cuts = false;  // most planes of a cell do not cut the polygon: it passes through unchanged
+            for (int k = 0; k < n && !cuts; ++k) cuts = sign * (poly[k][axis] - plane) < 0;
+            if (!cuts) continue;
             int m = 0;
             for (int k = 0; k < n; ++k) {
                 const double* a = poly[k];
@@ -131,13 +134,28 @@ struct Split {
 // two thirds of the build).  Same order as std::sort: the keys are plain integers.
 void sort_events(std::vector<Event>& ev, std::vector<Event>& tmp) {
     const size_t n = ev.size();
-    if (n < 4096) {
+    if (n < 64) {
         std::sort(ev.begin(), ev.end());
         return;
     }
     tmp.resize(n);
     Event* src = ev.data();
     Event* dst = tmp.data();
+    if (n < 4096) {
+        // Small and middle nodes (most of the calls): 7-bit digits, counters on the stack, and a pass in which all keys
+        // share the digit is skipped -- the events of a small cell agree in the upper bits of their positions.
+        for (int pass = 0; pass < 5; ++pass) {
+            const int shift = 7 * pass;
+            uint32_t count[129] = {0};
+            for (size_t i = 0; i < n; ++i) ++count[((src[i] >> shift) & 0x7Fu) + 1u];
+            if (count[((src[0] >> shift) & 0x7Fu) + 1u] == n) continue;
+            for (int k = 0; k < 128; ++k) count[k + 1] += count[k];
+            for (size_t i = 0; i < n; ++i) dst[count[(src[i] >> shift) & 0x7Fu]++] = src[i];
+            std::swap(src, dst);
+        }
+        if (src != ev.data()) ev.swap(tmp);
+        return;
+    }
     for (int pass = 0; pass < 3; ++pass) {
         const int shift = 12 * pass;
         uint32_t count[4097] = {0};
@@ -196,9 +214,8 @@ Split axis_split(const Box& cell, const std::vector<Ref>& refs, int axis, std::v
 
 // Best plane over the three axes; ties go to the lower axis, then the lower position (the order a sequential
 // sweep meets them in).  Big nodes run the axes as three tasks.
-Split find_split(const Box& cell, const std::vector<Ref>& refs, std::vector<Event>& ev) {
+Split find_split(const Box& cell, const std::vector<Ref>& refs) {
     Split per[3];
-    std::vector<Event> tmp;
     if (refs.size() >= (1u << 16)) {
         std::vector<Event> evs[3], tmps[3];
 #pragma omp taskgroup
@@ -209,7 +226,11 @@ Split find_split(const Box& cell, const std::vector<Ref>& refs, std::vector<Even
             }
         }
     } else {
+        // per-thread scratch: no scheduling point between here and the end of the three sweeps, and 1.8 M nodes would
+        // otherwise allocate and free two event arrays each
+        static thread_local std::vector<Event> ev, tmp;
         for (int axis = 0; axis < 3; ++axis) per[axis] = axis_split(cell, refs, axis, ev, tmp);
+        if (ev.capacity() > (1u << 20)) { std::vector<Event>().swap(ev); std::vector<Event>().swap(tmp); }
     }
     Split best;
     for (int axis = 0; axis < 3; ++axis)
@@ -218,10 +239,9 @@ Split find_split(const Box& cell, const std::vector<Ref>& refs, std::vector<Even
 }
 
 void build_node(const HostScene& s, std::vector<Node>& nodes, int me, std::vector<Ref>& refs, int depth, int maxDepth) {
-    std::vector<Event> ev;
     const size_t n = refs.size();
     Split sp;
-    if (n > 0 && depth < maxDepth) sp = find_split(nodes[me].cell, refs, ev);
+    if (n > 0 && depth < maxDepth) sp = find_split(nodes[me].cell, refs);
     if (sp.axis < 0 || sp.cost >= kIntersectCost * static_cast<float>(n)) {
         nodes[me].ids.reserve(n);
         for (const Ref& r : refs) nodes[me].ids.push_back(r.id);
