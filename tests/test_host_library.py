@@ -83,6 +83,25 @@ def test_stackless_layout_is_consistent(tracer, scenes, name, build_mode):
         tracer.check_stackless_layout()  # no geometry
 
 
+SAH_TREES = {"scene01": (1993, "bc608806e4beca86"), "scene01_lambert": (1993, "bc608806e4beca86"),
+             "scene02": (4041, "1d590ad416dbdf81"), "scene03": (12233, "d73efaab7c56034d")}
+
+
+@pytest.mark.parametrize("name", sorted(SAH_TREES))
+def test_sah_tree_is_frozen(tracer, scenes, name):
+    """The render path's own SAH tree (csrc/kd_build_sah.cpp), flattened: frozen so that work on the builder's speed
+    (radix passes, clipping shortcuts, task structure) cannot change the tree, which every measured number depends on."""
+    import hashlib
+    s = scenes[name]
+    tracer.create_geometry(s.verts, s.normals, s.tris, s.mats, tracer.BUILD_SAH)
+    t = tracer.get_tree()
+    h = hashlib.sha1()
+    for a in (t.left, t.right, t.aabb, t.split_axis, t.split_value, t.leaf_offset, t.leaf_count, t.leaf_ids):
+        h.update(np.ascontiguousarray(a).tobytes())
+    assert (len(t.left), h.hexdigest()[:16]) == SAH_TREES[name]
+    tracer.destroy_geometry()
+
+
 def test_scene_file_round_trip(tracer, scenes, tmp_path):
     p = str(tmp_path / "s.mcpt")
     scenes["scene02"].save(p)
