@@ -132,7 +132,7 @@ struct Split {
 // Events are 34-bit keys: three 12-bit passes of an LSD radix sort replace std::sort above a few thousand
 // events (1 M triangles: 2 M events per axis at the root, 170 ms -> 25 ms per axis on one core; the sorts were
 // two thirds of the build).  Same order as std::sort: the keys are plain integers.
-void sort_events(std::vector<Event>& ev, std::vector<Event>& tmp) {
+void sort_events(std::vector<Event>& ev, std::vector<Event>& tmp, const int base = 0) {
     const size_t n = ev.size();
     if (n < 64) {
         std::sort(ev.begin(), ev.end());
@@ -145,7 +145,7 @@ void sort_events(std::vector<Event>& ev, std::vector<Event>& tmp) {
         // Small and middle nodes (most of the calls): 7-bit digits, counters on the stack, and a pass in which all keys
         // share the digit is skipped -- the events of a small cell agree in the upper bits of their positions.
         for (int pass = 0; pass < 5; ++pass) {
-            const int shift = 7 * pass;
+            const int shift = base + 7 * pass;
             uint32_t count[129] = {0};
             for (size_t i = 0; i < n; ++i) ++count[((src[i] >> shift) & 0x7Fu) + 1u];
             if (count[((src[0] >> shift) & 0x7Fu) + 1u] == n) continue;
@@ -157,7 +157,7 @@ void sort_events(std::vector<Event>& ev, std::vector<Event>& tmp) {
         return;
     }
     for (int pass = 0; pass < 3; ++pass) {
-        const int shift = 12 * pass;
+        const int shift = base + 12 * pass;
         uint32_t count[4097] = {0};
         for (size_t i = 0; i < n; ++i) ++count[((src[i] >> shift) & 0xFFFu) + 1u];
         for (int k = 0; k < 4096; ++k) count[k + 1] += count[k];
@@ -168,31 +168,22 @@ void sort_events(std::vector<Event>& ev, std::vector<Event>& tmp) {
     ev.swap(tmp);
 }
 
-// Best plane of one axis: sweep over the sorted bound events (Wald & Havran 2006, section 4.2).
-Split axis_split(const Box& cell, const std::vector<Ref>& refs, int axis, std::vector<Event>& ev, std::vector<Event>& tmp) {
+// Sweep over bound events sorted by key (Wald & Havran 2006, section 4.2).  SHIFT exposes the 34-bit key: 0 for plain
+// events, kIdxBits for events that carry their reference's index in the low bits.
+constexpr int kIdxBits = 30;
+template <int SHIFT>
+Split sweep_events(const Box& cell, int axis, int n, const uint64_t* ev, size_t m) {
     Split best;
     if (!(cell.hi[axis] > cell.lo[axis])) return best;
     const float invSA = 1.0f / surface(cell);
-    const int n = static_cast<int>(refs.size());
-    ev.clear();
-    ev.reserve(2 * refs.size());
-    for (const Ref& r : refs) {
-        if (r.b.lo[axis] == r.b.hi[axis]) {
-            ev.push_back(make_event(r.b.lo[axis], 1u));
-        } else {
-            ev.push_back(make_event(r.b.lo[axis], 2u));
-            ev.push_back(make_event(r.b.hi[axis], 0u));
-        }
-    }
-    sort_events(ev, tmp);
     int nl = 0, nr = n;
-    for (size_t i = 0; i < ev.size();) {
-        const uint64_t group = ev[i] >> 2;
-        const float pos = event_pos(ev[i]);
+    for (size_t i = 0; i < m;) {
+        const uint64_t group = ev[i] >> (SHIFT + 2);
+        const float pos = event_pos(ev[i] >> SHIFT);
         int ends = 0, planar = 0, starts = 0;
-        while (i < ev.size() && (ev[i] >> 2) == group && (ev[i] & 3u) == 0u) { ++ends; ++i; }
-        while (i < ev.size() && (ev[i] >> 2) == group && (ev[i] & 3u) == 1u) { ++planar; ++i; }
-        while (i < ev.size() && (ev[i] >> 2) == group && (ev[i] & 3u) == 2u) { ++starts; ++i; }
+        while (i < m && (ev[i] >> (SHIFT + 2)) == group && ((ev[i] >> SHIFT) & 3u) == 0u) { ++ends; ++i; }
+        while (i < m && (ev[i] >> (SHIFT + 2)) == group && ((ev[i] >> SHIFT) & 3u) == 1u) { ++planar; ++i; }
+        while (i < m && (ev[i] >> (SHIFT + 2)) == group && ((ev[i] >> SHIFT) & 3u) == 2u) { ++starts; ++i; }
         nr -= planar + ends;
         if (pos > cell.lo[axis] && pos < cell.hi[axis]) {
             Box l = cell, r = cell;
@@ -210,6 +201,24 @@ Split axis_split(const Box& cell, const std::vector<Ref>& refs, int axis, std::v
         nl += starts + planar;
     }
     return best;
+}
+
+// Best plane of one axis: events of the node's references, sorted, swept.
+Split axis_split(const Box& cell, const std::vector<Ref>& refs, int axis, std::vector<Event>& ev, std::vector<Event>& tmp) {
+    if (!(cell.hi[axis] > cell.lo[axis])) return Split();
+    const int n = static_cast<int>(refs.size());
+    ev.clear();
+    ev.reserve(2 * refs.size());
+    for (const Ref& r : refs) {
+        if (r.b.lo[axis] == r.b.hi[axis]) {
+            ev.push_back(make_event(r.b.lo[axis], 1u));
+        } else {
+            ev.push_back(make_event(r.b.lo[axis], 2u));
+            ev.push_back(make_event(r.b.hi[axis], 0u));
+        }
+    }
+    sort_events(ev, tmp);
+    return sweep_events<0>(cell, axis, n, ev.data(), ev.size());
 }
 
 // Best plane over the three axes; ties go to the lower axis, then the lower position (the order a sequential
@@ -299,6 +308,152 @@ void build_node(const HostScene& s, std::vector<Node>& nodes, int me, std::vecto
 #pragma omp taskwait
 }
 
+// ---- sort once, keep sorted ------------------------------------------------------------------------------------
+// build_node sorts the bound events of a node afresh on every level: half of the build (6.0 of 11.5 G cycles on the
+// 1 M-triangle scene).  Above kResortBelow references a node instead INHERITS its three event lists already sorted
+// (Wald & Havran 2006, section 4.3): an event carries the index of its reference in the node's array; after the
+// split the events of references that go to one side only are appended to that child's list in order, the few
+// references the plane cuts get new events from their clipped bounds, sorted by themselves and merged in.  Same
+// references, same bounds, same event keys as build_node would produce, so the same sweep result and the same tree
+// (tests/test_host_library.py::test_sah_tree_is_frozen, tools/host_build_bench.cpp digest).
+using SEvent = uint64_t;  // (34-bit event key << kIdxBits) | index of the reference in the node's array
+constexpr size_t kResortBelow = 48;
+constexpr uint32_t kGone = 0xFFFFFFFFu;
+
+inline void push_ref_events(std::vector<SEvent>* ev, const Ref& r, uint32_t idx) {
+    for (int axis = 0; axis < 3; ++axis) {
+        if (r.b.lo[axis] == r.b.hi[axis]) {
+            ev[axis].push_back((make_event(r.b.lo[axis], 1u) << kIdxBits) | idx);
+        } else {
+            ev[axis].push_back((make_event(r.b.lo[axis], 2u) << kIdxBits) | idx);
+            ev[axis].push_back((make_event(r.b.hi[axis], 0u) << kIdxBits) | idx);
+        }
+    }
+}
+
+void build_node_sorted(const HostScene& s, std::vector<Node>& nodes, int me, std::vector<Ref>& refs, std::vector<SEvent>* ev, int depth,
+                       int maxDepth) {
+    const size_t n = refs.size();
+    if (n < kResortBelow) {
+        for (int axis = 0; axis < 3; ++axis) std::vector<SEvent>().swap(ev[axis]);
+        build_node(s, nodes, me, refs, depth, maxDepth);
+        return;
+    }
+    const bool big = n >= (1u << 16);
+    Split sp;
+    if (depth < maxDepth) {
+        Split per[3];
+        const Box cell = nodes[me].cell;
+        if (big) {
+#pragma omp taskgroup
+            for (int axis = 0; axis < 3; ++axis) {
+#pragma omp task shared(per, ev) firstprivate(axis, cell, n)
+                per[axis] = sweep_events<kIdxBits>(cell, axis, static_cast<int>(n), ev[axis].data(), ev[axis].size());
+            }
+        } else {
+            for (int axis = 0; axis < 3; ++axis) per[axis] = sweep_events<kIdxBits>(cell, axis, static_cast<int>(n), ev[axis].data(), ev[axis].size());
+        }
+        for (int axis = 0; axis < 3; ++axis)
+            if (per[axis].cost < sp.cost) sp = per[axis];
+    }
+    if (sp.axis < 0 || sp.cost >= kIntersectCost * static_cast<float>(n)) {
+        nodes[me].ids.reserve(n);
+        for (const Ref& r : refs) nodes[me].ids.push_back(r.id);
+        std::sort(nodes[me].ids.begin(), nodes[me].ids.end());
+        return;
+    }
+    const int a = sp.axis;
+    Box lc = nodes[me].cell, rc = nodes[me].cell;
+    lc.hi[a] = sp.plane;
+    rc.lo[a] = sp.plane;
+    // where each reference goes: its index in the left / right child (kGone = not there); cut references get new bounds
+    std::vector<Ref> lrefs, rrefs;
+    std::vector<uint32_t> li(n, kGone), ri(n, kGone);
+    std::vector<SEvent> newL[3], newR[3];
+    for (size_t i = 0; i < n; ++i) {
+        const Ref& r = refs[i];
+        if (r.b.lo[a] == r.b.hi[a] && r.b.lo[a] == sp.plane) {
+            if (sp.planarLeft) { li[i] = static_cast<uint32_t>(lrefs.size()); lrefs.push_back(r); }
+            else { ri[i] = static_cast<uint32_t>(rrefs.size()); rrefs.push_back(r); }
+        } else if (r.b.hi[a] <= sp.plane) {
+            li[i] = static_cast<uint32_t>(lrefs.size()); lrefs.push_back(r);
+        } else if (r.b.lo[a] >= sp.plane) {
+            ri[i] = static_cast<uint32_t>(rrefs.size()); rrefs.push_back(r);
+        } else {
+            Ref c{r.id, {}};
+            if (clipped_bounds(s, r.id, lc, c.b)) { push_ref_events(newL, c, static_cast<uint32_t>(lrefs.size())); lrefs.push_back(c); }
+            if (clipped_bounds(s, r.id, rc, c.b)) { push_ref_events(newR, c, static_cast<uint32_t>(rrefs.size())); rrefs.push_back(c); }
+        }
+    }
+    int lidx = -1, ridx = -1;
+#pragma omp critical(mcpt_sah_nodes)
+    if (nodes.size() + 2 <= nodes.capacity()) {
+        lidx = static_cast<int>(nodes.size());
+        ridx = lidx + 1;
+        nodes.emplace_back();
+        nodes.emplace_back();
+        nodes[lidx].cell = lc;
+        nodes[ridx].cell = rc;
+        nodes[me].axis = a;
+        nodes[me].plane = sp.plane;
+        nodes[me].left = lidx;
+        nodes[me].right = ridx;
+    }
+    if (lidx < 0) {  // node budget exhausted (pathological duplication): stop here, as build_node does
+        for (const Ref& r : lrefs) nodes[me].ids.push_back(r.id);
+        for (const Ref& r : rrefs) nodes[me].ids.push_back(r.id);
+        std::sort(nodes[me].ids.begin(), nodes[me].ids.end());
+        nodes[me].ids.erase(std::unique(nodes[me].ids.begin(), nodes[me].ids.end()), nodes[me].ids.end());
+        return;
+    }
+    // hand the sorted lists down: uncut references keep their events (new index), cut ones were regenerated above
+    std::vector<SEvent> L[3], R[3];
+    auto hand_down = [&](int axis) {
+        const SEvent idxMask = (SEvent(1) << kIdxBits) - 1;
+        std::vector<SEvent> l, r;
+        l.reserve(std::min(ev[axis].size(), 2 * lrefs.size()));  // at most two events per reference and axis
+        r.reserve(std::min(ev[axis].size(), 2 * rrefs.size()));
+        for (const SEvent e : ev[axis]) {
+            const uint32_t i = static_cast<uint32_t>(e & idxMask);
+            if (li[i] != kGone) l.push_back((e & ~idxMask) | li[i]);
+            else if (ri[i] != kGone) r.push_back((e & ~idxMask) | ri[i]);
+        }
+        std::vector<SEvent>().swap(ev[axis]);
+        auto byKey = [](SEvent x, SEvent y) { return (x >> kIdxBits) < (y >> kIdxBits); };
+        auto merge_in = [&](std::vector<SEvent>& base, std::vector<SEvent>& fresh, std::vector<SEvent>& out) {
+            if (fresh.empty()) { out.swap(base); return; }
+            std::sort(fresh.begin(), fresh.end());
+            out.resize(base.size() + fresh.size());
+            std::merge(base.begin(), base.end(), fresh.begin(), fresh.end(), out.begin(), byKey);
+        };
+        merge_in(l, newL[axis], L[axis]);
+        merge_in(r, newR[axis], R[axis]);
+    };
+    if (big) {
+#pragma omp taskgroup
+        for (int axis = 0; axis < 3; ++axis) {
+#pragma omp task shared(hand_down) firstprivate(axis)
+            hand_down(axis);
+        }
+    } else {
+        for (int axis = 0; axis < 3; ++axis) hand_down(axis);
+    }
+    std::vector<Ref>().swap(refs);
+    std::vector<uint32_t>().swap(li);
+    std::vector<uint32_t>().swap(ri);
+    const bool spawn = lrefs.size() + rrefs.size() > 4096;
+#pragma omp task shared(s, nodes) firstprivate(lidx, depth, maxDepth) if (spawn)
+    {
+        std::vector<Ref> mine;
+        mine.swap(lrefs);
+        std::vector<SEvent> mineEv[3];
+        for (int axis = 0; axis < 3; ++axis) mineEv[axis].swap(L[axis]);
+        build_node_sorted(s, nodes, lidx, mine, mineEv, depth + 1, maxDepth);
+    }
+    build_node_sorted(s, nodes, ridx, rrefs, R, depth + 1, maxDepth);
+#pragma omp taskwait
+}
+
 }  // namespace
 
 void build_sah_tree(const HostScene& scene, HostTree& out) {
@@ -322,9 +477,29 @@ void build_sah_tree(const HostScene& scene, HostTree& out) {
     nodes.reserve(6 * nT + 1024);
     nodes.emplace_back();
     nodes[0].cell = root;
+    const char* resort = std::getenv("MCPT_SAH_RESORT");  // A/B knob: the re-sorting builder on every level
+    if (resort && *resort == '1') {
 #pragma omp parallel
 #pragma omp single
-    build_node(scene, nodes, 0, refs, 0, maxDepth);
+        build_node(scene, nodes, 0, refs, 0, maxDepth);
+    } else {
+        std::vector<SEvent> ev[3];
+        for (int axis = 0; axis < 3; ++axis) ev[axis].reserve(2 * nT);
+        for (size_t t = 0; t < nT; ++t) push_ref_events(ev, refs[t], static_cast<uint32_t>(t));
+#pragma omp parallel
+#pragma omp single
+        {
+#pragma omp taskgroup
+            for (int axis = 0; axis < 3; ++axis) {
+#pragma omp task shared(ev) firstprivate(axis)
+                {
+                    std::vector<SEvent> tmp;
+                    sort_events(ev[axis], tmp, kIdxBits);
+                }
+            }
+            build_node_sorted(scene, nodes, 0, refs, ev, 0, maxDepth);
+        }
+    }
     if (std::getenv("MCPT_BUILD_TIMING")) std::fprintf(stderr, "sah: recursion %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
 
     // breadth-first renumbering, children adjacent (same layout as the reference flatten)
