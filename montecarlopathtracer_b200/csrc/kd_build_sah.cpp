@@ -298,7 +298,8 @@ void build_node(const HostScene& s, std::vector<Node>& nodes, int me, std::vecto
         return;
     }
     const bool spawn = lrefs.size() + rrefs.size() > 4096;
-#pragma omp task shared(s, nodes) firstprivate(li, depth, maxDepth) if (spawn)
+    // lrefs is shared on purpose (it would be copied into the task otherwise): this frame waits at the taskwait below
+#pragma omp task shared(s, nodes, lrefs) firstprivate(li, depth, maxDepth) if (spawn)
     {
         std::vector<Ref> mine;
         mine.swap(lrefs);
@@ -442,7 +443,7 @@ void build_node_sorted(const HostScene& s, std::vector<Node>& nodes, int me, std
     std::vector<uint32_t>().swap(li);
     std::vector<uint32_t>().swap(ri);
     const bool spawn = lrefs.size() + rrefs.size() > 4096;
-#pragma omp task shared(s, nodes) firstprivate(lidx, depth, maxDepth) if (spawn)
+#pragma omp task shared(s, nodes, lrefs, L) firstprivate(lidx, depth, maxDepth) if (spawn)
     {
         std::vector<Ref> mine;
         mine.swap(lrefs);
