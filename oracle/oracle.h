@@ -7,10 +7,13 @@
  * the checker or the timed CPU baseline -- never as part of the product path.
  *
  * Parity status: the host half (OBJ ingest, tree build, flatten) is PINNED against the
- * reference's own code compiled here (oracle/_ref/libmcpt_ref.so, see ref_bridge.cpp);
- * the device half (rtx.hlsl) cannot be compiled or run on this box (no HLSL compiler,
- * no D3D) and the reference ships no golden vectors, so the shader restatement is
- * "parity unpinned" beyond line-by-line correspondence, which each function cites.
+ * reference's own code compiled here (oracle/_ref/libmcpt_ref.so, see ref_bridge.cpp).
+ * Device half: rtx.hlsl itself cannot be compiled or run on this box (no HLSL compiler, no
+ * graphics stack) and the reference ships no golden vectors; the three BSDF samplers
+ * (rtx.hlsl:213-302) are PINNED bit for bit to the reference's own CUDA/Utils.hpp:46-137 --
+ * the same math, compiled unmodified on the host into oracle/_ref/libmcpt_refcv.so -- and the
+ * determinant order to Matrix33f::det; traversal, path loop and ray generation correspond
+ * statement by statement (each function cites its lines) and are frozen by tests/golden/.
  */
 #ifndef MCPT_ORACLE_H
 #define MCPT_ORACLE_H
@@ -91,6 +94,14 @@ void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t
 void oracle_sample_hemi(float u1, float u2, const float n[3], float out[3]);
 void oracle_sample_phong(float u1, float u2, const float n[3], const float dir[3], float Ns, float out[3]);
 void oracle_sample_fresnel(float u, const float n[3], const float dir[3], float Tr, float Ni, float out[3]);
+/* The CUDA twin's sampleFresnel and normalize (CVMCTracer/CVMCTracer/CUDA/Utils.hpp:97-137, :27-34). */
+void oracle_sample_fresnel_twin(float u, const float n[3], const float dir[3], float Tr, float Ni, float out[3]);
+void oracle_normalize_twin(float v[3]);
+/* n tuples at once; the uniforms are used exactly as given (raw floats, any grid).
+ * kind 0 hemi (u: 2/call), 1 phong (u: 2/call, par0 = Ns), 2 fresnel (u: 1/call, par0 = Tr, par1 = Ni),
+ * 3 the twin's fresnel. */
+void oracle_sample_batch(int kind, int64_t n, const float* u, const float* normals, const float* dirs,
+                         const float* par0, const float* par1, float* out);
 
 #ifdef __cplusplus
 }

@@ -310,32 +310,58 @@ void oracle_frame_seeds(int first, int count, uint32_t* out) { frame_seeds(first
 void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { philox4x32_10(ctr, key, out); }
 
 namespace {
-// Feeds fixed uniforms into the samplers: mode-1 Rng whose buffer is preloaded.
-Rng fixed_rng(float a, float b) {
+// Feeds fixed uniforms into the samplers exactly as given (no quantisation: the reference's own streams --
+// curand_uniform, Park-Miller / 0x7FFFFFFF -- do not live on Philox's 2^-24 grid).
+struct FixedRng {
+    float u[2];
     Rng r;
-    r.mode = 1;
-    // invert u = ((x >> 8) + 1) * 2^-24  ->  x = (u * 2^24 - 1) << 8
-    auto enc = [](float u) { return (static_cast<uint32_t>(u * 16777216.0f) - 1u) << 8; };
-    r.buf[0] = 0; r.buf[1] = enc(a); r.buf[2] = enc(b); r.buf[3] = 0;
-    r.draw = 1;  // next() reads buf[1], buf[2] without regenerating
-    return r;
-}
+    FixedRng(float a, float b) {
+        u[0] = a; u[1] = b;
+        r.mode = 2; r.fixed = u; r.draw = 0;
+    }
+};
 }  // namespace
 
 void oracle_sample_hemi(float u1, float u2, const float n[3], float out[3]) {
-    Rng r = fixed_rng(u1, u2);
-    V3 o = sample_hemi(r, {n[0], n[1], n[2]});
+    FixedRng f(u1, u2);
+    V3 o = sample_hemi(f.r, {n[0], n[1], n[2]});
     out[0] = o.x; out[1] = o.y; out[2] = o.z;
 }
 void oracle_sample_phong(float u1, float u2, const float n[3], const float dir[3], float Ns, float out[3]) {
-    Rng r = fixed_rng(u1, u2);
-    V3 o = sample_phong(r, {n[0], n[1], n[2]}, {dir[0], dir[1], dir[2]}, Ns);
+    FixedRng f(u1, u2);
+    V3 o = sample_phong(f.r, {n[0], n[1], n[2]}, {dir[0], dir[1], dir[2]}, Ns);
     out[0] = o.x; out[1] = o.y; out[2] = o.z;
 }
 void oracle_sample_fresnel(float u, const float n[3], const float dir[3], float Tr, float Ni, float out[3]) {
-    Rng r = fixed_rng(u, u);
-    V3 o = sample_fresnel(r, {n[0], n[1], n[2]}, {dir[0], dir[1], dir[2]}, Tr, Ni);
+    FixedRng f(u, u);
+    V3 o = sample_fresnel(f.r, {n[0], n[1], n[2]}, {dir[0], dir[1], dir[2]}, Tr, Ni);
     out[0] = o.x; out[1] = o.y; out[2] = o.z;
+}
+void oracle_sample_fresnel_twin(float u, const float n[3], const float dir[3], float Tr, float Ni, float out[3]) {
+    FixedRng f(u, u);
+    V3 o = sample_fresnel_twin(f.r, {n[0], n[1], n[2]}, {dir[0], dir[1], dir[2]}, Tr, Ni);
+    out[0] = o.x; out[1] = o.y; out[2] = o.z;
+}
+void oracle_normalize_twin(float v[3]) {
+    V3 o = normalize_twin({v[0], v[1], v[2]});
+    v[0] = o.x; v[1] = o.y; v[2] = o.z;
+}
+
+// Batched forms (n tuples) for the parity tests: u is 2 floats per call (hemi, phong) or 1 (fresnel).
+// kind: 0 hemi, 1 phong (par0 = Ns), 2 fresnel (par0 = Tr, par1 = Ni), 3 the twin's fresnel (Utils.hpp:97-137).
+void oracle_sample_batch(int kind, int64_t n, const float* u, const float* normals, const float* dirs,
+                         const float* par0, const float* par1, float* out) {
+    for (int64_t i = 0; i < n; ++i) {
+        const float* nn = normals + 3 * i;
+        const float* dd = dirs ? dirs + 3 * i : nullptr;
+        float* o = out + 3 * i;
+        switch (kind) {
+            case 0: oracle_sample_hemi(u[2 * i], u[2 * i + 1], nn, o); break;
+            case 1: oracle_sample_phong(u[2 * i], u[2 * i + 1], nn, dd, par0[i], o); break;
+            case 2: oracle_sample_fresnel(u[i], nn, dd, par0[i], par1[i], o); break;
+            default: oracle_sample_fresnel_twin(u[i], nn, dd, par0[i], par1[i], o); break;
+        }
+    }
 }
 
 }  // extern "C"

@@ -60,8 +60,10 @@ struct Tally {
 // mode 1: Philox4x32-10, key = (pixel, seed), counter = (sample, slot, block, 0);
 //         slot 0 = camera jitter, slot b+1 = scattering event b; draws are taken
 //         sequentially inside a slot; u = ((x >> 8) + 1) * 2^-24 in (0,1].
+// mode 2: a fixed list of uniforms handed in by a test (`fixed`), returned as they are.
 struct Rng {
     int mode = 0;
+    const float* fixed = nullptr;
     uint32_t sd = 0;
     uint32_t key[2] = {0, 0};
     uint32_t sample = 0, slot = 0, draw = 0;
@@ -78,6 +80,7 @@ Hit intersect(const Scene& scene, V3 from, V3 dir, Tally& tally);
 V3 sample_hemi(Rng& rng, V3 normal);
 V3 sample_phong(Rng& rng, V3 normal, V3 dir, float Ns);
 V3 sample_fresnel(Rng& rng, V3 normal, V3 dir, float Tr, float Ni);
+V3 sample_fresnel_twin(Rng& rng, V3 normal, V3 dir, float Tr, float Ni);
 V3 sample_mc(const Scene& scene, Rng& rng, V3 from, V3 dir, uint32_t depth, Tally& tally);
 V3 sample_mc_twin(const Scene& scene, Rng& rng, V3 from, V3 dir, uint32_t maxDepth, float illum, Tally& tally);
 V3 normalize_twin(V3 v);

@@ -214,6 +214,10 @@ class ReferenceCV:
         L.refcv_copy.argtypes = [_vp] * 5
         L.refcv_det33.argtypes = [_vp]
         L.refcv_det33.restype = C.c_float
+        L.refcv_sample_hemi.argtypes = [C.c_ulonglong, C.c_int, _vp, _vp, _vp]
+        L.refcv_sample_phong.argtypes = [C.c_ulonglong, C.c_int, _vp, _vp, _vp, _vp, _vp]
+        L.refcv_sample_fresnel.argtypes = [C.c_ulonglong, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp]
+        L.refcv_normalize.argtypes = [_vp]
         self.L = L
 
     @staticmethod
@@ -233,6 +237,39 @@ class ReferenceCV:
         self.L.refcv_copy(h, _ptr(s.verts), _ptr(s.normals), _ptr(s.tris), _ptr(s.mats))
         self.L.refcv_free(h)
         return s
+
+    # ---- CUDA/Utils.hpp:46-137, the reference's own samplers compiled on the host -------------------
+    # Each returns (directions (n,3), the uniforms curand_uniform handed the sampler in each call).
+    def sample_hemi(self, seed: int, normals: np.ndarray):
+        normals = np.ascontiguousarray(normals, np.float32)
+        n = len(normals)
+        out, u = np.empty((n, 3), np.float32), np.empty((n, 2), np.float32)
+        self.L.refcv_sample_hemi(seed, n, _ptr(normals), _ptr(out), _ptr(u))
+        return out, u
+
+    def sample_phong(self, seed: int, normals: np.ndarray, dirs: np.ndarray, Ns: np.ndarray):
+        normals = np.ascontiguousarray(normals, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        Ns = np.ascontiguousarray(Ns, np.uint32)
+        n = len(normals)
+        out, u = np.empty((n, 3), np.float32), np.empty((n, 2), np.float32)
+        self.L.refcv_sample_phong(seed, n, _ptr(normals), _ptr(dirs), _ptr(Ns), _ptr(out), _ptr(u))
+        return out, u
+
+    def sample_fresnel(self, seed: int, normals: np.ndarray, dirs: np.ndarray, Tr: np.ndarray, Ni: np.ndarray):
+        normals = np.ascontiguousarray(normals, np.float32)
+        dirs = np.ascontiguousarray(dirs, np.float32)
+        Tr = np.ascontiguousarray(Tr, np.float32)
+        Ni = np.ascontiguousarray(Ni, np.float32)
+        n = len(normals)
+        out, u = np.empty((n, 3), np.float32), np.empty(n, np.float32)
+        self.L.refcv_sample_fresnel(seed, n, _ptr(normals), _ptr(dirs), _ptr(Tr), _ptr(Ni), _ptr(out), _ptr(u))
+        return out, u
+
+    def normalize(self, v) -> np.ndarray:
+        v = np.array(v, np.float32).reshape(3)
+        self.L.refcv_normalize(_ptr(v))
+        return v
 
     def det33(self, m) -> np.float32:
         m = np.ascontiguousarray(m, np.float32).reshape(9)
@@ -266,6 +303,9 @@ class Oracle:
         L.oracle_sample_hemi.argtypes = [C.c_float, C.c_float, _vp, _vp]
         L.oracle_sample_phong.argtypes = [C.c_float, C.c_float, _vp, _vp, C.c_float, _vp]
         L.oracle_sample_fresnel.argtypes = [C.c_float, _vp, _vp, C.c_float, C.c_float, _vp]
+        L.oracle_sample_fresnel_twin.argtypes = [C.c_float, _vp, _vp, C.c_float, C.c_float, _vp]
+        L.oracle_normalize_twin.argtypes = [_vp]
+        L.oracle_sample_batch.argtypes = [C.c_int, C.c_int64] + [_vp] * 6
         self.L = L
 
     def cfg(self, width, height, spp, depth, **kw) -> Cfg:
@@ -292,6 +332,23 @@ class Oracle:
         out = np.empty(4, np.uint32)
         self.L.oracle_philox4x32_10(_ptr(ctr), _ptr(key), _ptr(out))
         return out
+
+    HEMI, PHONG, FRESNEL, FRESNEL_TWIN = 0, 1, 2, 3
+
+    def sample_batch(self, kind: int, u, normals, dirs=None, par0=None, par1=None) -> np.ndarray:
+        """The restated samplers (rtx.hlsl:213-302; kind 3: the twin's Utils.hpp:97-137) on n tuples; the uniforms
+        `u` ((n,2) for hemi/phong, (n,) for fresnel) are consumed exactly as given."""
+        c = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+        u, normals, dirs, par0, par1 = c(u), c(normals), c(dirs), c(par0), c(par1)
+        n = len(normals)
+        out = np.empty((n, 3), np.float32)
+        self.L.oracle_sample_batch(kind, n, _ptr(u), _ptr(normals), _ptr(dirs), _ptr(par0), _ptr(par1), _ptr(out))
+        return out
+
+    def normalize_twin(self, v) -> np.ndarray:
+        v = np.array(v, np.float32).reshape(3)
+        self.L.oracle_normalize_twin(_ptr(v))
+        return v
 
     def primary_rays(self, cfg: Cfg, frame: int = 0) -> np.ndarray:
         w = (cfg.x1 - cfg.x0) if cfg.x1 > cfg.x0 else cfg.width

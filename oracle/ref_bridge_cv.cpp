@@ -9,7 +9,15 @@
 // It also exposes Matrix33f::det (Framework/Math.hpp:157-185), the one explicit determinant order the
 // reference gives, so the oracle's triangle test can be pinned against it.
 // Used by tests/ to pin libmcpt's MCPT_LOADER_OBJREADER convention.
+//
+// Third part: the REFERENCE'S OWN BSDF SAMPLERS, CUDA/Utils.hpp:46-137 (sampleHemi, samplePhong,
+// sampleFresnel; the same math as rtx.hlsl:213-302), compiled unmodified for the HOST: without nvcc
+// cuda_runtime.h defines __device__ / __inline__ away and curand_kernel.h's XORWOW generator
+// (curand_init, curand_uniform) is plain C.  Each call's uniforms are recovered by replaying a copy of
+// the curandState, so that the oracle's restatement (shader_restate.cpp) can be fed the very same
+// numbers and compared bit for bit (tests/test_oracle_pins.py).
 #include <Framework/ObjReader.hpp>
+#include <CUDA/Utils.hpp>
 
 #include <cstdint>
 #include <cstring>
@@ -75,6 +83,59 @@ void refcv_copy(void* h, float* verts, float* normals, uint32_t* tris, float* ma
 float refcv_det33(const float* m) {
     PW::Math::Matrix33f M(m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], m[8]);
     return M.det();
+}
+
+// ---- CUDA/Utils.hpp:46-137 on the host ----------------------------------------------------------
+// n calls on one XORWOW stream (curand_init(seed, 0, 0), as rayTraceKernel seeds it, CUTracer.cu:186-187).
+// normals / dirs: 3 floats per call; out: 3 floats per call; uniforms: the 2 (hemi, phong) or 1 (fresnel)
+// numbers curand_uniform handed the sampler in that call, in draw order.
+void refcv_sample_hemi(unsigned long long seed, int n, const float* normals, float* out, float* uniforms) {
+    curandState rng;
+    curand_init(seed, 0, 0, &rng);
+    for (int i = 0; i < n; ++i) {
+        curandState replay = rng;
+        uniforms[2 * i] = curand_uniform(&replay);
+        uniforms[2 * i + 1] = curand_uniform(&replay);
+        const PWVector3f nrm(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]);
+        const PWVector3f o = PW::CUDA::sampleHemi(&rng, nrm);
+        out[3 * i] = o.x; out[3 * i + 1] = o.y; out[3 * i + 2] = o.z;
+    }
+}
+
+void refcv_sample_phong(unsigned long long seed, int n, const float* normals, const float* dirs, const unsigned* Ns,
+                        float* out, float* uniforms) {
+    curandState rng;
+    curand_init(seed, 0, 0, &rng);
+    for (int i = 0; i < n; ++i) {
+        curandState replay = rng;
+        uniforms[2 * i] = curand_uniform(&replay);
+        uniforms[2 * i + 1] = curand_uniform(&replay);
+        const PWVector3f nrm(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]);
+        const PWVector3f d(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
+        const PWVector3f o = PW::CUDA::samplePhong(&rng, nrm, d, Ns[i]);
+        out[3 * i] = o.x; out[3 * i + 1] = o.y; out[3 * i + 2] = o.z;
+    }
+}
+
+void refcv_sample_fresnel(unsigned long long seed, int n, const float* normals, const float* dirs, const float* Tr,
+                          const float* Ni, float* out, float* uniforms) {
+    curandState rng;
+    curand_init(seed, 0, 0, &rng);
+    for (int i = 0; i < n; ++i) {
+        curandState replay = rng;
+        uniforms[i] = curand_uniform(&replay);
+        const PWVector3f nrm(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]);
+        const PWVector3f d(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]);
+        const PWVector3f o = PW::CUDA::sampleFresnel(&rng, nrm, d, Tr[i], Ni[i]);
+        out[3 * i] = o.x; out[3 * i + 1] = o.y; out[3 * i + 2] = o.z;
+    }
+}
+
+// CUDA/Utils.hpp:27-34 normalize, :12-15 dot (the twin's path loop uses both, CUTracer.cu:126,152).
+void refcv_normalize(float v[3]) {
+    PWVector3f a(v[0], v[1], v[2]);
+    PW::CUDA::normalize(a);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z;
 }
 
 }  // extern "C"

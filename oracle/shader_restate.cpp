@@ -10,8 +10,12 @@
 //   * 1/x and a/b are IEEE divides, sqrt is IEEE, pow/sin/cos are libm's;
 //   * HLSL min/max ignore NaN -> fminf/fmaxf;
 //   * normalize(v) = v * (1 / sqrt(dot(v,v))), dot sums left to right.
-// "Parity unpinned": the reference ships no golden outputs for this shader and it cannot
-// be compiled here; correspondence is by citation, statement by statement.
+// Parity status: rtx.hlsl itself cannot be compiled here (no HLSL compiler, no graphics stack) and the
+// reference ships no golden outputs.  What IS pinned to the reference's own code: the three samplers are bit-equal
+// to CVMCTracer/CVMCTracer/CUDA/Utils.hpp:46-137 -- the same math as rtx.hlsl:213-302, compiled unmodified on the
+// host into oracle/_ref/libmcpt_refcv.so -- on the uniforms that code itself drew (tests/test_oracle_pins.py);
+// the determinant order to Matrix33f::det; the tree to KDTree.hpp.  The traversal/path loop (:144-211, :304-371)
+// and ray generation (:373-398) correspond by citation, statement by statement.
 #include <cmath>
 
 #include "oracle_internal.h"
@@ -101,6 +105,7 @@ void philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]
 
 float Rng::next() {
     if (mode == 0) return rand_gen(sd);
+    if (mode == 2) return fixed[draw++];
     if ((draw & 3u) == 0u) {
         uint32_t ctr[4] = {sample, slot, draw >> 2, 0u};
         philox4x32_10(ctr, key, buf);
@@ -294,6 +299,34 @@ V3 normalize_twin(V3 v) {
     return v;
 }
 
+// CUDA/Utils.hpp:97-137: the twin's sampleFresnel.  Same branches as rtx.hlsl:213-251, but the result is normalised
+// only in the two refract branches, by Utils.hpp:27-34's divide-by-length (the reflect branches :120,:134 return
+// indir - 2 (indir.n) n as it is), where the shader normalises every branch with rsqrt (:250).
+// Pinned bit for bit against the reference's own Utils.hpp compiled on the host (tests/test_oracle_pins.py).
+V3 sample_fresnel_twin(Rng& rng, V3 normal, V3 dir, float Tr, float Ni) {
+    float x = rng.next();
+    V3 outdir;
+    float ndoti = dot(dir, normal);
+    Tr = Tr * (1 - powf(1 - fabsf(ndoti), 5));
+    if (x < Tr) {
+        if (ndoti <= 0) {
+            float alpha = -ndoti / Ni - sqrtf(1 - (1 - ndoti * ndoti) / Ni / Ni);
+            outdir = normalize_twin(normal * alpha + dir / Ni);
+        } else {
+            float test = 1 - (1 - ndoti * ndoti) * Ni * Ni;
+            if (test < 0) {
+                outdir = dir - normal * dot(dir, normal) * 2;
+            } else {
+                float alpha = -ndoti * Ni + sqrtf(test);
+                outdir = normalize_twin(normal * alpha + dir * Ni);
+            }
+        }
+    } else {
+        outdir = dir - normal * dot(dir, normal) * 2;
+    }
+    return outdir;
+}
+
 // CUTracer.cu:98-177 over the same scene tables (the twin binds one material per OBJ group; the loader
 // already gives every triangle its group's material, CUTracer.cu:300-308).  Same samplers as rtx.hlsl
 // (Utils.hpp:46-137 is the same math) except that samplePhong takes Ns as an unsigned (Utils.hpp:72).
@@ -313,7 +346,7 @@ V3 sample_mc_twin(const Scene& scene, Rng& rng, V3 from, V3 dir, uint32_t maxDep
                     load3(scene.normals, tri.n[2]) * hit.gamma;
         normal = normalize_twin(normal);
         if (m.Tr > 0) {
-            dir = sample_fresnel(rng, normal, dir, m.Tr, m.Ni);
+            dir = sample_fresnel_twin(rng, normal, dir, m.Tr, m.Ni);
             color = color * V3{m.Kd[0], m.Kd[1], m.Kd[2]};  // :131-133, the tint rtx.hlsl:345 comments out
         } else if (m.Ns > 1) {
             dir = sample_phong(rng, normal, dir, static_cast<float>(static_cast<uint32_t>(m.Ns)));

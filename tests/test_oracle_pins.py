@@ -212,3 +212,102 @@ def test_cuda_twin_mode_semantics(oracle, scenes):
     # the MCRT estimator on the same scene may take up to 3 * depth + 1 rays and applies roulette: a different sample set
     s2, _, _, c2 = sc.render(oracle.cfg(40, 30, 8, 7, rng_mode=1, seed=2))
     assert c2.rays != c.rays
+
+
+# ---- the shading half, pinned to the reference's own code ---------------------------------------------------
+# CVMCTracer/CVMCTracer/CUDA/Utils.hpp:46-137 is the same math as rtx.hlsl:213-302 and compiles
+# unmodified on the host (oracle/ref_bridge_cv.cpp).  The bridge hands back the uniforms each call drew from the
+# reference's own cuRAND stream; the restatement is fed those numbers as they are.
+def _sampler_inputs(n, seed):
+    """Unit normals and incoming directions incl. the rotation's special cases (|n.y +- 1| < FLT_EPSILON,
+    rtx.hlsl:262-267 / :287-292), near-special normals, grazing and normal incidence."""
+    g = np.random.default_rng(seed)
+    nrm = g.normal(size=(n, 3))
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    nrm = nrm.astype(np.float32)
+    nrm[0], nrm[1] = [0, 1, 0], [0, -1, 0]
+    nrm[2] = [0, np.float32(1) - np.float32(2.0 ** -24), 0]      # inside the epsilon
+    nrm[3] = [3e-4, np.sqrt(1 - 9e-8), 0]                         # just outside it
+    nrm[4] = [0, -1 + 2.0 ** -24, 1e-5]
+    nrm[5], nrm[6], nrm[7] = [1, 0, 0], [0, 0, -1], [0.6, 0.0, 0.8]
+    d = g.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d = d.astype(np.float32)
+    d[8] = -nrm[8]                                                # normal incidence
+    t = np.cross(nrm[9], [0.3, 0.5, 0.8]); t /= np.linalg.norm(t)
+    d[9] = (t + 1e-3 * nrm[9]).astype(np.float32)                # grazing
+    return nrm, d
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+@pytest.fixture(scope="module")
+def refcv():
+    from oracle.pyoracle import ReferenceCV, build
+    build()
+    if not ReferenceCV.available():
+        pytest.skip("oracle/_ref/libmcpt_refcv.so not built (needs /root/reference)")
+    return ReferenceCV()
+
+
+def test_sample_hemi_bit_equal_to_reference_utils_hpp(oracle, refcv):
+    """rtx.hlsl:278-302 restated == CUDA/Utils.hpp:46-70 compiled from /root/reference, bit for bit."""
+    nrm, _ = _sampler_inputs(30000, 11)
+    want, u = refcv.sample_hemi(1234, nrm)
+    assert (u > 0).all() and (u <= 1).all() and len(np.unique(u)) > 59000
+    got = oracle.sample_batch(oracle.HEMI, u, nrm)
+    assert np.array_equal(_bits(got), _bits(want))
+
+
+def test_sample_phong_bit_equal_to_reference_utils_hpp(oracle, refcv):
+    """rtx.hlsl:253-276 restated == CUDA/Utils.hpp:72-95 (Ns arrives as PWuint there: integral exponents)."""
+    nrm, d = _sampler_inputs(30000, 12)
+    Ns = np.random.default_rng(3).choice([2, 5, 10, 20, 50, 1000], 30000).astype(np.uint32)
+    want, u = refcv.sample_phong(99, nrm, d, Ns)
+    got = oracle.sample_batch(oracle.PHONG, u, nrm, d, Ns.astype(np.float32))
+    assert np.array_equal(_bits(got), _bits(want))
+
+
+def test_sample_fresnel_twin_bit_equal_to_reference_utils_hpp(oracle, refcv):
+    """CUDA/Utils.hpp:97-137 restated (sample_fresnel_twin: normalised in the refract branches only) is bit-equal to
+    the reference's code; the shader form (rtx.hlsl:213-251, normalize() on every branch, :250) takes the same
+    branch for every tuple and differs from it only by that normalisation (a few ulp)."""
+    n = 40000
+    nrm, d = _sampler_inputs(n, 13)
+    g = np.random.default_rng(4)
+    Tr = g.choice([0.9, 0.5, 1.0, 0.1], n).astype(np.float32)
+    Ni = g.choice([1.5, 1.33, 2.4, 1.0], n).astype(np.float32)
+    want, u = refcv.sample_fresnel(7, nrm, d, Tr, Ni)
+    got = oracle.sample_batch(oracle.FRESNEL_TWIN, u, nrm, d, Tr, Ni)
+    assert np.array_equal(_bits(got), _bits(want))
+    hlsl = oracle.sample_batch(oracle.FRESNEL, u, nrm, d, Tr, Ni)
+    assert np.abs(hlsl - want).max() < 1e-6
+    # every branch of :218-249 is exercised: refraction entering / leaving, total internal reflection, reflection
+    c = (d * nrm).sum(1)
+    refl = (d - 2 * c[:, None] * nrm)
+    is_refl = np.abs(want - refl).max(1) < 1e-5
+    assert (is_refl & (c > 0)).sum() > 1000 and (~is_refl & (c > 0)).sum() > 1000 and (~is_refl & (c <= 0)).sum() > 1000
+    tir = (c > 0) & (1 - (1 - c * c) * Ni * Ni < 0) & (u < Tr * (1 - (1 - np.abs(c)) ** 5))
+    assert tir.sum() > 500 and is_refl[tir].all()
+
+
+def test_normalize_twin_bit_equal_to_reference_utils_hpp(oracle, refcv):
+    """CUDA/Utils.hpp:27-34 (divide by the length unless it is below FLT_EPSILON): the twin's path loop normalises the
+    shading normal and the camera ray with it (CUTracer.cu:126,210)."""
+    g = np.random.default_rng(8)
+    for v in list(g.normal(size=(2000, 3)).astype(np.float32)) + [np.float32([0, 0, 0]), np.float32([1e-8, 0, 0]), np.float32([3e-8, 4e-8, 0])]:
+        assert np.array_equal(_bits(oracle.normalize_twin(v)), _bits(refcv.normalize(v)))
+
+
+def test_sampler_api_takes_uniforms_as_they_are(oracle):
+    """The reference streams are not on Philox's 2^-24 grid: curand_uniform is k 2^-32 + 2^-33, Park-Miller sd / (2^31 - 1).
+    oracle_sample_* must use the float it is given (round 1 snapped it to 2^-24)."""
+    n = np.float32([[0.36, 0.48, 0.8]])
+    u = np.float32(np.float32(0.3) + np.float32(2.0 ** -25))   # one ulp above 0.3: off the 2^-24 grid
+    a = oracle.sample_batch(oracle.HEMI, np.float32([[u, 0.25]]), n)
+    b = oracle.sample_batch(oracle.HEMI, np.float32([[0.3, 0.25]]), n)
+    assert not np.array_equal(_bits(a), _bits(b))
+    # cos(theta) about the normal is sqrt(1 - u) for the float given
+    assert abs(float(a[0] @ n[0]) - np.sqrt(1 - float(u))) < 1e-6
