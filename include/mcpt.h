@@ -68,7 +68,17 @@ enum {
     MCPT_FLAG_MOMENTS = 2u,    /* also accumulate per-pixel sum of squares                    */
     MCPT_FLAG_NO_JITTER = 4u,  /* pixel-corner rays ("bias = 0"), for the intersection gate   */
     MCPT_FLAG_REF_TRAVERSAL = 8u, /* render with the reference-order AABB traversal instead of the KD traversal */
-    MCPT_FLAG_SIMPLE_KERNEL = 16u /* one-ray-per-iteration kernel instead of the warp-voted state machine (A/B) */
+    MCPT_FLAG_SIMPLE_KERNEL = 16u, /* one-ray-per-iteration kernel instead of the warp-voted state machine (A/B) */
+    MCPT_FLAG_RENDER_ARITHMETIC = 32u /* mcpt_primary_rays only: the rays as the render kernels compute them (hardware
+                                        rsqrt, folded camera factors) instead of the IEEE form that is bit-equal to the oracle */
+};
+
+/* Sampler kinds of mcpt_sample_batch. */
+enum {
+    MCPT_SAMPLE_HEMI = 0,         /* rtx.hlsl:278-302 = CUDA/Utils.hpp:46-70                      */
+    MCPT_SAMPLE_PHONG = 1,        /* rtx.hlsl:253-276 = CUDA/Utils.hpp:72-95   (par0 = Ns)        */
+    MCPT_SAMPLE_FRESNEL = 2,      /* rtx.hlsl:213-251                          (par0 = Tr, par1 = Ni) */
+    MCPT_SAMPLE_FRESNEL_TWIN = 3  /* CUDA/Utils.hpp:97-137: normalised in the refract branches only */
 };
 
 /* Intersection kernels selectable through mcpt_intersect_batch. */
@@ -168,8 +178,17 @@ int mcpt_intersect_batch(const float* rays, int64_t n, int variant, int32_t* tri
                          float* beta, float* gamma);
 int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, void* dev_tri,
                                 void* dev_t, void* dev_beta, void* dev_gamma, void* stream);
-/* Primary rays of one sample index exactly as the render kernel generates them (6 floats/pixel). */
+/* Primary rays of one sample index (6 floats/pixel): rtx.hlsl:376-398 in IEEE arithmetic, bit-equal to the oracle's;
+ * with MCPT_FLAG_RENDER_ARITHMETIC in cfg->flags the rays exactly as the render kernels generate them (same map, one
+ * host-computed factor per axis and the hardware rsqrt: a few ulp from the IEEE form). */
 int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays);
+/* ---- sampler parity hook (rtx.hlsl:213-302 / CUDA/Utils.hpp:46-137) ------------------------ */
+/* Runs the device BSDF samplers on n tuples.  u: 2 uniforms per tuple, used as given (fresnel takes the first);
+ * normals, dirs: 3 floats per tuple (dirs may be NULL for MCPT_SAMPLE_HEMI); par0/par1 per tuple as the kind needs;
+ * out: 3 floats per tuple.  render_arithmetic = 0: the IEEE forms (compared with the oracle to the ulp);
+ * 1: the forms the render kernels run (MUFU rsqrt/sqrt/rcp/lg2/ex2, sincospif). */
+int mcpt_sample_batch(int kind, int64_t n, const float* u, const float* normals, const float* dirs,
+                      const float* par0, const float* par1, int render_arithmetic, float* out);
 
 /* Work counters of one traversal variant over a host ray batch: out = {nodes popped, leaves (KD) or
  * boxes (reference order) entered, triangle tests}.  Feeds the roofline's algorithmic-work figures. */

@@ -4,8 +4,10 @@
 
 nvcc cross-compiles for sm_100a without a GPU.  Flags that matter:
   -gencode arch=compute_100a,code=sm_100a   B200 only, no PTX fallback for other parts
-  -fmad=false, no -use_fast_math            IEEE mul/add/div/sqrt, never contracted: the
-                                            intersection gate is bit-exact against the CPU oracle
+  no -use_fast_math; -fmad=false for parity.cu (the kernels compared bit for bit with the CPU oracle);
+  -fmad=true for launch.cu                  the render kernels' triangle test is explicit round-to-nearest
+                                            intrinsics (bit-exact whatever the flag); shading and the walk's
+                                            steering may contract (+2.6 % at K2, profiles/r2_tuning.md)
   -ffp-contract=off (host)                  the KD builder and the triangle pre-computation must
                                             round like the reference's x86 build
 """
@@ -18,18 +20,24 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
-OBJDIR = os.path.join(HERE, "build")
-LIB = os.path.join(LIBDIR, "libmcpt.so")
+# MCPT_BUILD_NAME=x builds lib/libmcpt_x.so next to the shipped library (A/B builds for the GPU box: tracer.py loads
+# the library named by MCPT_LIB); extra nvcc flags for launch.cu in MCPT_NVCC_EXTRA.
+_NAME = os.environ.get("MCPT_BUILD_NAME", "")
+OBJDIR = os.path.join(HERE, "build" + ("_" + _NAME if _NAME else ""))
+LIB = os.path.join(LIBDIR, "libmcpt" + ("_" + _NAME if _NAME else "") + ".so")
 CLI = os.path.join(LIBDIR, "mcpt_cli")
 
 NVCC = os.environ.get("MCPT_NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = "/usr/bin/g++"
 CUDA_INC = "/usr/local/cuda/include"
 
-CU_SOURCES = ["launch.cu"]
+CU_SOURCES = ["launch.cu", "parity.cu"]
 CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "kd_ropes.cpp", "obj_loader.cpp", "image_io.cpp", "abi_geometry.cpp", "abi_render.cpp"]
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-fmad=false", "-diag-suppress=549",
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-diag-suppress=549",
               "-Xcompiler", "-fPIC", "-ccbin", CXX]
+# parity.cu (kernels compared bit for bit with the CPU oracle) is never contracted; launch.cu (render kernels: the
+# triangle test is explicit _rn intrinsics, shading uses the hardware units) takes MCPT_FMAD (profiles/r2_tuning.md).
+FMAD = {"launch.cu": os.environ.get("MCPT_FMAD", "true"), "parity.cu": "false"}
 CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-Wall", "-I" + CUDA_INC]
 
 
@@ -56,7 +64,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         o = os.path.join(OBJDIR, src + ".o")
         objs.append(o)
         if force or _newer(o, [os.path.join(CSRC, src)] + hdrs):
-            cmd = [NVCC] + NVCC_FLAGS + ["-c", os.path.join(CSRC, src), "-o", o]
+            cmd = [NVCC] + NVCC_FLAGS + ["-fmad=" + FMAD[src], "-c", os.path.join(CSRC, src), "-o", o]
+            if src == "launch.cu":
+                cmd[1:1] = os.environ.get("MCPT_NVCC_EXTRA", "").split()
             if os.environ.get("MCPT_TUNE"):       # tuning build: every render_kernel_sm variant (launch.cu)
                 cmd.insert(1, "-DMCPT_TUNE")
             if verbose:
@@ -71,7 +81,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         subprocess.check_call([NVCC, "-shared", "-ccbin", CXX, "-o", LIB] + objs +
                               ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp", "-Wno-deprecated-gpu-targets"])
     cli_src = os.path.join(CSRC, "cli.cpp")
-    if force or _newer(CLI, [cli_src, LIB] + hdrs):   # headless driver, links only against the C ABI
+    if not _NAME and (force or _newer(CLI, [cli_src, LIB] + hdrs)):   # headless driver, links only against the C ABI
         subprocess.check_call([CXX, "-std=c++17", "-O2", cli_src, "-o", CLI, "-L" + LIBDIR, "-lmcpt", "-Wl,-rpath,$ORIGIN"])
     return LIB
 

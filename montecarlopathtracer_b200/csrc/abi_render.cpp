@@ -290,10 +290,42 @@ int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays) 
     DCamera cam = make_camera(cfg->eye, cfg->at, cfg->up, cfg->fovy, cfg->width, cfg->height, cfg->tracer_mode == MCPT_TRACER_CUDA_TWIN ? 1 : 0);
     c.counters.launches = 0;
     if ((e = launch_primary_rays(cam, cfg->width, cfg->height, sample, cfg->seed, (cfg->flags & MCPT_FLAG_NO_JITTER) ? 0u : 1u,
-                                 cfg->rng_mode, frameSeed, c.d_rays.ptr, c.stream, &c.counters.launches)) != cudaSuccess)
+                                 cfg->rng_mode, frameSeed, (cfg->flags & MCPT_FLAG_RENDER_ARITHMETIC) != 0, c.d_rays.ptr, c.stream,
+                                 &c.counters.launches)) != cudaSuccess)
         return fail_cuda(e, "primary rays launch");
     if ((e = cudaMemcpyAsync(host_rays, c.d_rays.ptr, 6 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H rays");
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "primary rays");
+    return MCPT_OK;
+}
+
+int mcpt_sample_batch(int kind, int64_t n, const float* u, const float* normals, const float* dirs, const float* par0,
+                      const float* par1, int render_arithmetic, float* out) {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (kind < MCPT_SAMPLE_HEMI || kind > MCPT_SAMPLE_FRESNEL_TWIN) return fail(MCPT_ERR_INVALID, "unknown sampler kind");
+    if (n < 0 || (n > 0 && (!u || !normals || !out))) return fail(MCPT_ERR_INVALID, "bad sampler batch");
+    if (n > 0 && kind != MCPT_SAMPLE_HEMI && !dirs) return fail(MCPT_ERR_INVALID, "this sampler needs incoming directions");
+    if (n > 0 && kind != MCPT_SAMPLE_HEMI && !par0) return fail(MCPT_ERR_INVALID, "missing sampler parameter (Ns / Tr)");
+    if (n > 0 && kind >= MCPT_SAMPLE_FRESNEL && !par1) return fail(MCPT_ERR_INVALID, "missing sampler parameter (Ni)");
+    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    if (n == 0) return MCPT_OK;
+    const size_t N = static_cast<size_t>(n);
+    // one scratch buffer: u (2N) | normals (3N) | dirs (3N) | par0 (N) | par1 (N) | out (3N)
+    cudaError_t e;
+    if ((e = c.d_rays.ensure(13 * N)) != cudaSuccess) return fail_cuda(e, "alloc sampler batch");
+    float* d = c.d_rays.ptr;
+    float *du = d, *dn = d + 2 * N, *dd = d + 5 * N, *dp0 = d + 8 * N, *dp1 = d + 9 * N, *dout = d + 10 * N;
+    auto up = [&](float* dst, const float* src, size_t cnt) {
+        return src ? cudaMemcpyAsync(dst, src, cnt * sizeof(float), cudaMemcpyHostToDevice, c.stream) : cudaSuccess;
+    };
+    if ((e = up(du, u, 2 * N)) != cudaSuccess || (e = up(dn, normals, 3 * N)) != cudaSuccess || (e = up(dd, dirs, 3 * N)) != cudaSuccess ||
+        (e = up(dp0, par0, N)) != cudaSuccess || (e = up(dp1, par1, N)) != cudaSuccess)
+        return fail_cuda(e, "H2D sampler batch");
+    c.counters.launches = 0;
+    if ((e = launch_sample(kind, n, du, dn, dirs ? dd : nullptr, dp0, dp1, render_arithmetic != 0, dout, c.stream, &c.counters.launches)) != cudaSuccess)
+        return fail_cuda(e, "sampler launch");
+    if ((e = cudaMemcpyAsync(out, dout, 3 * N * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H");
+    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "sampler batch");
     return MCPT_OK;
 }
 

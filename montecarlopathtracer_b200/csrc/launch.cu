@@ -1,9 +1,11 @@
-// Kernel instantiations and launch wrappers.  Compile for sm_100a with -fmad=false and WITHOUT
-// -use_fast_math: the intersection-parity gate and the per-sample agreement with the CPU oracle
-// rely on IEEE mul/add/div/sqrt that are not contracted.
+// Render-kernel instantiations and launch wrappers (sm_100a).  The triangle test is written in explicit
+// round-to-nearest intrinsics (intersect.cuh: tri_test) and is bit-exact whatever this file's flags; shading and
+// the walk's steering use the hardware units (MCPT_FAST_SHADE).  The kernels whose outputs are
+// compared bit for bit with the CPU oracle live in parity.cu (always -fmad=false).
 #include "launch.h"
 
 #include "../../include/mcpt.h"
+#include "hooks.cuh"
 #include "render_sm.cuh"
 
 #include <type_traits>
@@ -19,58 +21,6 @@
 namespace mcpt {
 
 namespace {
-
-__global__ void __launch_bounds__(256) intersect_kernel(const DScene sc, const float* __restrict__ rays, int64_t n,
-                                                        int variant, int32_t* __restrict__ tri, float* __restrict__ t,
-                                                        float* __restrict__ beta, float* __restrict__ gamma) {
-    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float* r = rays + 6 * i;
-    const float ox = __ldg(r), oy = __ldg(r + 1), oz = __ldg(r + 2), dx = __ldg(r + 3), dy = __ldg(r + 4), dz = __ldg(r + 5);
-    const Hit h = variant == MCPT_ISECT_ROPES ? intersect_ropes(sc, ox, oy, oz, dx, dy, dz)
-                  : variant == MCPT_ISECT_KD  ? intersect_kd(sc, ox, oy, oz, dx, dy, dz)
-                                              : intersect_ref(sc, ox, oy, oz, dx, dy, dz);
-    tri[i] = static_cast<int32_t>(h.tri);
-    if (t) t[i] = h.t;
-    if (beta) beta[i] = h.beta;
-    if (gamma) gamma[i] = h.gamma;
-}
-
-// Work counters of one traversal variant over a ray batch: {nodes popped, leaves/boxes entered,
-// triangle tests} -- the per-ray figures the roofline's algorithmic work is stated in.
-__global__ void __launch_bounds__(256) tally_kernel(const DScene sc, const float* __restrict__ rays, int64_t n, int variant,
-                                                    unsigned long long* __restrict__ out) {
-    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    TraversalTally tally;
-    if (i < n) {
-        const float* r = rays + 6 * i;
-        if (variant == MCPT_ISECT_ROPES) intersect_ropes(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
-        else if (variant == MCPT_ISECT_KD) intersect_kd(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
-        else intersect_ref(sc, r[0], r[1], r[2], r[3], r[4], r[5], &tally);
-    }
-    uint32_t a = tally.popped, b = tally.entered, c = tally.tris;
-    for (int off = 16; off > 0; off >>= 1) {
-        a += __shfl_xor_sync(0xFFFFFFFFu, a, off); b += __shfl_xor_sync(0xFFFFFFFFu, b, off); c += __shfl_xor_sync(0xFFFFFFFFu, c, off);
-    }
-    if ((threadIdx.x & 31) == 0) { atomicAdd(out, (unsigned long long)a); atomicAdd(out + 1, (unsigned long long)b); atomicAdd(out + 2, (unsigned long long)c); }
-}
-
-template <class RNG>
-__global__ void __launch_bounds__(256) primary_rays_kernel(const DCamera cam, int width, int height, uint32_t sample,
-                                                           uint32_t seed, uint32_t jitter, uint32_t frameSeed,
-                                                           float* __restrict__ rays) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= static_cast<uint32_t>(width) * static_cast<uint32_t>(height)) return;
-    const uint32_t px = i % static_cast<uint32_t>(width), py = i / static_cast<uint32_t>(width);
-    RNG rng;
-    rng.start(i, seed, sample, frameSeed);
-    float u1 = 0.5f, u2 = 0.5f;
-    if (jitter) { u1 = rng.next(); u2 = rng.next(); }
-    F3 o, d;
-    camera_ray(cam, width, height, px, py, u1, u2, o, d);
-    float* r = rays + 6 * static_cast<size_t>(i);
-    r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = d.x; r[4] = d.y; r[5] = d.z;
-}
 
 __global__ void __launch_bounds__(256) reduce_slices_kernel(const float4* __restrict__ slices, int chunks, size_t pixels,
                                                             float4* __restrict__ dst, int accumulate) {
@@ -101,32 +51,6 @@ __global__ void __launch_bounds__(256) fp32_peak_kernel(float* __restrict__ out,
         a4 = __fmaf_rn(a4, x, y); a5 = __fmaf_rn(a5, x, y); a6 = __fmaf_rn(a6, x, y); a7 = __fmaf_rn(a7, x, y);
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
-}
-
-// div3_rn against __fdiv_rn on pseudo-random operands (Philox), counters[0] = mismatching quotients,
-// counters[1] = quadruples that took the shared-reciprocal branch.
-__global__ void __launch_bounds__(256) selfcheck_div3_kernel(long long n, uint32_t seed, int spread, unsigned long long* counters) {
-    unsigned long long bad = 0, fast = 0;
-    for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n; i += gridDim.x * 256ll) {
-        uint32_t o[4], e[4];
-        philox4x32_10(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32), 0u, 0u, seed, 0x51ED270Bu, o);
-        philox4x32_10(static_cast<uint32_t>(i), static_cast<uint32_t>(i >> 32), 1u, 0u, seed, 0x51ED270Bu, e);
-        float v[4];
-        for (int k = 0; k < 4; ++k) {
-            // random sign and mantissa, exponent uniform in [-spread, spread]
-            const int ex = static_cast<int>(e[k] % static_cast<uint32_t>(2 * spread + 1)) - spread;
-            v[k] = __uint_as_float((o[k] & 0x807FFFFFu) | (static_cast<uint32_t>(127 + ex) << 23));
-        }
-        float a0, a1, a2;
-        div3_rn(v[0], v[1], v[2], v[3], a0, a1, a2);
-        const float b0 = __fdiv_rn(v[0], v[3]), b1 = __fdiv_rn(v[1], v[3]), b2 = __fdiv_rn(v[2], v[3]);
-        bad += (__float_as_uint(a0) != __float_as_uint(b0)) + (__float_as_uint(a1) != __float_as_uint(b1)) +
-               (__float_as_uint(a2) != __float_as_uint(b2));
-        fast += div3_guard<false>(v[0], v[1], v[2], v[3]) ? 1u : 0u;
-    }
-    bad = __reduce_add_sync(0xFFFFFFFFu, static_cast<unsigned>(bad));
-    fast = __reduce_add_sync(0xFFFFFFFFu, static_cast<unsigned>(fast));
-    if ((threadIdx.x & 31u) == 0u) { atomicAdd(counters, bad); atomicAdd(counters + 1, fast); }
 }
 
 template <class RNG, bool KD, bool NEE, bool MOMENTS>
@@ -219,38 +143,30 @@ cudaError_t launch_finalize(const float4* sum, size_t pixels, float* rgb, cudaSt
     return cudaGetLastError();
 }
 
-cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int variant, int32_t* tri, float* t,
-                             float* beta, float* gamma, cudaStream_t stream, uint32_t* launches) {
-    if (n <= 0) return cudaSuccess;
-    if (launches) ++*launches;
-    intersect_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(sc, rays, n, variant, tri, t, beta, gamma);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_tally(const DScene& sc, const float* rays, int64_t n, int variant, unsigned long long* out, cudaStream_t stream) {
-    if (n <= 0) return cudaSuccess;
-    tally_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(sc, rays, n, variant, out);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_selfcheck_div3(long long n, uint32_t seed, int spread, unsigned long long* counters, cudaStream_t stream) {
-    selfcheck_div3_kernel<<<148 * 8, 256, 0, stream>>>(n, seed, spread, counters);
-    return cudaGetLastError();
-}
-
 cudaError_t launch_fp32_peak(float* scratch, int blocks, int iters, cudaStream_t stream) {
     fp32_peak_kernel<<<blocks, 256, 0, stream>>>(scratch, iters, 0.999f, 0.001f);
     return cudaGetLastError();
 }
 
 cudaError_t launch_primary_rays(const DCamera& cam, int width, int height, int sample, uint32_t seed, uint32_t jitter,
-                                int rng_mode, uint32_t frame_seed, float* rays, cudaStream_t stream, uint32_t* launches) {
+                                int rng_mode, uint32_t frame_seed, bool render_path, float* rays, cudaStream_t stream,
+                                uint32_t* launches) {
     if (launches) ++*launches;
+    if (!render_path) return launch_primary_rays_exact(cam, width, height, sample, seed, jitter, rng_mode, frame_seed, rays, stream);
     const unsigned blocks = (static_cast<unsigned>(width) * static_cast<unsigned>(height) + 255u) / 256u;
     if (rng_mode == MCPT_RNG_REFERENCE)
-        primary_rays_kernel<RngReference><<<blocks, 256, 0, stream>>>(cam, width, height, sample, seed, jitter, frame_seed, rays);
+        primary_rays_kernel<RngReference, !kFastShade><<<blocks, 256, 0, stream>>>(cam, width, height, sample, seed, jitter, frame_seed, rays);
     else
-        primary_rays_kernel<RngPhilox><<<blocks, 256, 0, stream>>>(cam, width, height, sample, seed, jitter, frame_seed, rays);
+        primary_rays_kernel<RngPhilox, !kFastShade><<<blocks, 256, 0, stream>>>(cam, width, height, sample, seed, jitter, frame_seed, rays);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sample(int kind, int64_t n, const float* u, const float* normals, const float* dirs, const float* par0,
+                          const float* par1, bool render_path, float* out, cudaStream_t stream, uint32_t* launches) {
+    if (n <= 0) return cudaSuccess;
+    if (launches) ++*launches;
+    if (!render_path) return launch_sample_exact(kind, n, u, normals, dirs, par0, par1, out, stream);
+    sample_kernel<kFastShade><<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(kind, n, u, normals, dirs, par0, par1, out);
     return cudaGetLastError();
 }
 

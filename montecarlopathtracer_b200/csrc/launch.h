@@ -42,8 +42,18 @@ cudaError_t launch_finalize(const float4* sum, size_t pixels, float* rgb, cudaSt
 cudaError_t launch_intersect(const DScene& sc, const float* rays, int64_t n, int variant, int32_t* tri, float* t,
                              float* beta, float* gamma, cudaStream_t stream, uint32_t* launches);
 
+// render_path: the rays as the render kernels generate them (hardware rsqrt, folded factors) instead of the IEEE form.
 cudaError_t launch_primary_rays(const DCamera& cam, int width, int height, int sample, uint32_t seed, uint32_t jitter,
-                                int rng_mode, uint32_t frame_seed, float* rays, cudaStream_t stream, uint32_t* launches);
+                                int rng_mode, uint32_t frame_seed, bool render_path, float* rays, cudaStream_t stream,
+                                uint32_t* launches);
+cudaError_t launch_primary_rays_exact(const DCamera& cam, int width, int height, int sample, uint32_t seed, uint32_t jitter,
+                                      int rng_mode, uint32_t frame_seed, float* rays, cudaStream_t stream);  // parity.cu
+
+// BSDF samplers on n tuples (kind: 0 hemi, 1 phong, 2 fresnel, 3 twin fresnel); render_path as above.
+cudaError_t launch_sample(int kind, int64_t n, const float* u, const float* normals, const float* dirs, const float* par0,
+                          const float* par1, bool render_path, float* out, cudaStream_t stream, uint32_t* launches);
+cudaError_t launch_sample_exact(int kind, int64_t n, const float* u, const float* normals, const float* dirs,
+                                const float* par0, const float* par1, float* out, cudaStream_t stream);  // parity.cu
 
 cudaError_t launch_tally(const DScene& sc, const float* rays, int64_t n, int variant, unsigned long long* out3, cudaStream_t stream);
 

@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256) render_kernel(const RenderParams p) {
                     lastWasNee = false;
                     if (mKd.w > 0) {  // Tr > 0, :342-346
                         const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);
-                        dir = sample_fresnel(rng, normal, dir, mKd.w, mKs.w);
+                        dir = sample_fresnel(rng, normal, dir, mKd.w, mKs.w, p.twin != 0u);  // twin: Utils.hpp:97-137
                         if (p.twin) thr = thr * f3(mKd.x, mKd.y, mKd.z);  // CUTracer.cu:131-133
                     } else if (mKa.w > 1) {  // Ns > 1, :348-352
                         const float4 mKs = ldg4(p.sc.mats + 3 * mat + 2);

@@ -28,42 +28,44 @@ __device__ __forceinline__ float dot(F3 a, F3 b) { return a.x * b.x + a.y * b.y 
 #define MCPT_FAST_SHADE 1
 #endif
 // 1/sqrt(x) and sqrt(x) for shading directions: one MUFU instruction each instead of ~10-20 (IEEE sqrt + IEEE divide).
+// FAST is a template parameter (default: the build's MCPT_FAST_SHADE) so that the sampler parity hook
+// (mcpt_sample_batch) can run both forms from one library.
+constexpr bool kFastShade = MCPT_FAST_SHADE != 0;
+template <bool FAST = kFastShade>
 __device__ __forceinline__ float shade_rsqrt(float x) {
-#if MCPT_FAST_SHADE
-    float y;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-#else
-    return 1.0f / sqrtf(x);
-#endif
+    if (FAST) {
+        float y;
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+        return y;
+    }
+    return __fdiv_rn(1.0f, __fsqrt_rn(x));
 }
+template <bool FAST = kFastShade>
 __device__ __forceinline__ float shade_sqrt(float x) {
-#if MCPT_FAST_SHADE
-    float y;
-    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-#else
-    return sqrtf(x);
-#endif
+    if (FAST) {
+        float y;
+        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+        return y;
+    }
+    return __fsqrt_rn(x);
 }
 // sin and cos of 2 pi y
+template <bool FAST = kFastShade>
 __device__ __forceinline__ void shade_sincos_2pi(float y, float* s, float* c) {
-#if MCPT_FAST_SHADE
-    sincospif(2.0f * y, s, c);
-#else
-    sincosf(2 * 3.14159265358979323846f * y, s, c);
-#endif
+    if (FAST) sincospif(2.0f * y, s, c);
+    else sincosf(__fmul_rn(__fmul_rn(2.0f, 3.14159265358979323846f), y), s, c);
 }
+template <bool FAST = kFastShade>
 __device__ __forceinline__ float shade_rcp(float x) {
-#if MCPT_FAST_SHADE
-    float y;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-#else
-    return 1.0f / x;
-#endif
+    if (FAST) {
+        float y;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+        return y;
+    }
+    return __fdiv_rn(1.0f, x);
 }
-__device__ __forceinline__ F3 normalize(F3 v) { return v * shade_rsqrt(dot(v, v)); }
+template <bool FAST = kFastShade>
+__device__ __forceinline__ F3 normalize(F3 v) { return v * shade_rsqrt<FAST>(dot(v, v)); }
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based: key = (pixel, seed),
 // counter = (sample, slot, block, 0); slot 0 = camera jitter, slot b+1 = scattering event b,
@@ -139,41 +141,48 @@ struct RngReference {
 #define MCPT_PI 3.14159265358979323846f
 #define MCPT_EPS 1.192092896e-07f
 
-// rtx.hlsl:213-251
-template <class RNG>
-__device__ __forceinline__ F3 sample_fresnel(RNG& rng, F3 normal, F3 dir, float Tr, float Ni) {
+// rtx.hlsl:213-251.  TWIN: CUDA/Utils.hpp:97-137 -- the same branches, but only the two refract branches normalise
+// (by Utils.hpp:27-34's divide by the length unless it is below FLT_EPSILON); the reflect branches return
+// dir - 2 (dir.n) n as it is.
+template <class RNG, bool FAST = kFastShade>
+__device__ __forceinline__ F3 sample_fresnel(RNG& rng, F3 normal, F3 dir, float Tr, float Ni, bool twin = false) {
     const float x = rng.next();
     F3 outdir;
+    bool refracted = false;
     const float ndoti = dot(dir, normal);
-#if MCPT_FAST_SHADE
-    // pow(c, 5) by three products; the quotients by Ni as products with one reciprocal (each within an ulp or two of
-    // the IEEE sequence below, which costs ~50 + 5 x 10 instructions)
-    const float c1 = 1 - fabsf(ndoti), c2 = c1 * c1;
-    Tr = Tr * (1 - c2 * c2 * c1);
-    if (x < Tr) {
-        float rNi;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rNi) : "f"(Ni));
-        if (ndoti <= 0) {
-            const float alpha = -ndoti * rNi - shade_sqrt(1 - (1 - ndoti * ndoti) * rNi * rNi);
-            outdir = normal * alpha + dir * rNi;
-        } else {
-            const float test = 1 - (1 - ndoti * ndoti) * Ni * Ni;
-            if (test < 0) {
-                outdir = dir - normal * ndoti * 2;
+    if (FAST) {
+        // pow(c, 5) by three products; the quotients by Ni as products with one reciprocal (each within an ulp or two of
+        // the IEEE sequence below, which costs ~50 + 5 x 10 instructions)
+        const float c1 = 1 - fabsf(ndoti), c2 = c1 * c1;
+        Tr = Tr * (1 - c2 * c2 * c1);
+        if (x < Tr) {
+            const float rNi = shade_rcp<true>(Ni);
+            if (ndoti <= 0) {
+                const float alpha = -ndoti * rNi - shade_sqrt<true>(1 - (1 - ndoti * ndoti) * rNi * rNi);
+                outdir = normal * alpha + dir * rNi;
+                refracted = true;
             } else {
-                const float alpha = -ndoti * Ni + shade_sqrt(test);
-                outdir = normal * alpha + dir * Ni;
+                const float test = 1 - (1 - ndoti * ndoti) * Ni * Ni;
+                if (test < 0) {
+                    outdir = dir - normal * ndoti * 2;
+                } else {
+                    const float alpha = -ndoti * Ni + shade_sqrt<true>(test);
+                    outdir = normal * alpha + dir * Ni;
+                    refracted = true;
+                }
             }
+        } else {
+            outdir = dir - normal * ndoti * 2;
         }
-    } else {
-        outdir = dir - normal * ndoti * 2;
+        if (twin && !refracted) return outdir;
+        return normalize<true>(outdir);
     }
-#else
     Tr = Tr * (1 - powf(1 - fabsf(ndoti), 5.0f));
     if (x < Tr) {
         if (ndoti <= 0) {
             const float alpha = -ndoti / Ni - sqrtf(1 - (1 - ndoti * ndoti) / Ni / Ni);
             outdir = normal * alpha + dir / Ni;
+            refracted = true;
         } else {
             const float test = 1 - (1 - ndoti * ndoti) * Ni * Ni;
             if (test < 0) {
@@ -181,28 +190,33 @@ __device__ __forceinline__ F3 sample_fresnel(RNG& rng, F3 normal, F3 dir, float 
             } else {
                 const float alpha = -ndoti * Ni + sqrtf(test);
                 outdir = normal * alpha + dir * Ni;
+                refracted = true;
             }
         }
     } else {
         outdir = dir - normal * dot(dir, normal) * 2;
     }
-#endif
-    return normalize(outdir);
+    if (twin) {
+        if (refracted) {
+            const float len = sqrtf(dot(outdir, outdir));
+            if (fabsf(len) > MCPT_EPS) outdir = outdir / len;
+        }
+        return outdir;
+    }
+    return normalize<false>(outdir);
 }
 
 // Rotation of a +Y-centred lobe direction onto `normal` (rtx.hlsl:262-274 / :287-300).
 // divideByInvlen selects samplePhong's `d.z / invlen` against sampleHemi's `d.z * (1/invlen)`.
+template <bool FAST = kFastShade>
 __device__ __forceinline__ F3 rotate_to(F3 d, F3 normal, bool divideByInvlen) {
     if (fabsf(normal.y + 1) < MCPT_EPS) return -d;
     if (fabsf(normal.y - 1) >= MCPT_EPS) {
-        const float invlen = shade_rsqrt(1.0f - normal.y * normal.y);
+        const float invlen = shade_rsqrt<FAST>(1.0f - normal.y * normal.y);
         F3 o;
         o.x = (normal.z * d.x + normal.x * normal.y * d.z) * invlen + normal.x * d.y;
-#if MCPT_FAST_SHADE
-        o.y = normal.y * d.y - d.z * ((1.0f - normal.y * normal.y) * invlen);  // 1 / invlen
-#else
-        o.y = divideByInvlen ? (normal.y * d.y - d.z / invlen) : (normal.y * d.y - d.z * (1.0f / invlen));
-#endif
+        if (FAST) o.y = normal.y * d.y - d.z * ((1.0f - normal.y * normal.y) * invlen);  // 1 / invlen
+        else o.y = divideByInvlen ? (normal.y * d.y - d.z / invlen) : (normal.y * d.y - d.z * (1.0f / invlen));
         o.z = (-normal.x * d.x + normal.z * normal.y * d.z) * invlen + normal.z * d.y;
         return o;
     }
@@ -210,36 +224,43 @@ __device__ __forceinline__ F3 rotate_to(F3 d, F3 normal, bool divideByInvlen) {
 }
 
 // rtx.hlsl:253-276
-template <class RNG>
+template <class RNG, bool FAST = kFastShade>
 __device__ __forceinline__ F3 sample_phong(RNG& rng, F3 normal, F3 dir, float Ns) {
     const float x = rng.next();
     const float y = rng.next();
-#if MCPT_FAST_SHADE
-    // x^(1/(Ns+1)) = 2^(log2(x) / (Ns+1)): x in (0,1], the exponent in (0, 1/2): MUFU.LG2's absolute error (2^-22) is
-    // scaled down by it, the result is within ~1 ulp of powf's
-    float rN;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rN) : "f"(Ns + 1));
-    const float cosT = exp2f(__log2f(x) * rN);
-#else
-    const float cosT = powf(x, 1.0f / (Ns + 1));
-#endif
-    const float sinT = shade_sqrt(fmaxf(1 - cosT * cosT, 0.0f));
+    float cosT;
+    if (FAST) {
+        // x^(1/(Ns+1)) = 2^(log2(x) / (Ns+1)): x in (0,1], the exponent in (0, 1/2): MUFU.LG2's absolute error (2^-22) is
+        // scaled down by it, the result is within ~1 ulp of powf's
+        cosT = exp2f(__log2f(x) * shade_rcp<true>(Ns + 1));
+    } else {
+        cosT = powf(x, 1.0f / (Ns + 1));
+    }
+    // FAST clamps the radicand: MUFU arithmetic can land cosT an ulp above 1 (the IEEE form cannot: powf(x <= 1, e > 0) <= 1)
+    const float sinT = FAST ? shade_sqrt<true>(fmaxf(1 - cosT * cosT, 0.0f)) : sqrtf(1 - cosT * cosT);
     float s, c;
-    shade_sincos_2pi(y, &s, &c);
-    const F3 halfdir = rotate_to(f3(sinT * c, cosT, sinT * s), normal, true);
+    shade_sincos_2pi<FAST>(y, &s, &c);
+    const F3 halfdir = rotate_to<FAST>(f3(sinT * c, cosT, sinT * s), normal, true);
     return dir - halfdir * dot(dir, halfdir) * 2;
 }
 
 // rtx.hlsl:278-302
-template <class RNG>
+template <class RNG, bool FAST = kFastShade>
 __device__ __forceinline__ F3 sample_hemi(RNG& rng, F3 normal) {
     const float x = rng.next();
     const float y = rng.next();
-    const float sinT = shade_sqrt(x);
-    const float cosT = shade_sqrt(1 - x);
+    const float sinT = shade_sqrt<FAST>(x);
+    const float cosT = shade_sqrt<FAST>(1 - x);
     float s, c;
-    shade_sincos_2pi(y, &s, &c);
-    return rotate_to(f3(sinT * c, cosT, sinT * s), normal, false);
+    shade_sincos_2pi<FAST>(y, &s, &c);
+    return rotate_to<FAST>(f3(sinT * c, cosT, sinT * s), normal, false);
 }
+
+// Fixed uniforms handed in by the sampler parity hook (mcpt_sample_batch).
+struct RngFixed {
+    float u0, u1;
+    int i;
+    __device__ __forceinline__ float next() { return i++ == 0 ? u0 : u1; }
+};
 
 }  // namespace mcpt

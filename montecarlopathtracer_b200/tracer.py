@@ -15,13 +15,14 @@ from dataclasses import dataclass
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libmcpt.so")
+LIB_PATH = os.environ.get("MCPT_LIB") or os.path.join(HERE, "lib", "libmcpt.so")   # MCPT_LIB: an A/B build (build.py)
 
 # enums of include/mcpt.h
 BUILD_REFERENCE, BUILD_SAH = 0, 1
 LOADER_TINYOBJ, LOADER_OBJREADER = 0, 1
 RNG_PHILOX, RNG_REFERENCE = 0, 1
-FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL, FLAG_SIMPLE_KERNEL = 1, 2, 4, 8, 16
+FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL, FLAG_SIMPLE_KERNEL, FLAG_RENDER_ARITHMETIC = 1, 2, 4, 8, 16, 32
+SAMPLE_HEMI, SAMPLE_PHONG, SAMPLE_FRESNEL, SAMPLE_FRESNEL_TWIN = 0, 1, 2, 3
 ISECT_REFERENCE, ISECT_KD, ISECT_ROPES = 0, 1, 2
 TRACER_MCRT, TRACER_CUDA_TWIN = 0, 1
 ERR_NO_DEVICE = 4
@@ -89,6 +90,7 @@ def lib() -> C.CDLL:
     L.mcpt_intersect_batch.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp]
     L.mcpt_intersect_batch_device.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp]
     L.mcpt_primary_rays.argtypes = [C.POINTER(RenderCfg), C.c_int, _vp]
+    L.mcpt_sample_batch.argtypes = [C.c_int, C.c_int64, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]
     L.mcpt_get_counters.argtypes = [C.POINTER(Counters)]
     L.mcpt_traversal_stats.argtypes = [_vp, C.c_int64, C.c_int, _vp]
     L.mcpt_measure_fp32_peak.argtypes = [C.POINTER(C.c_double)]
@@ -257,6 +259,20 @@ def primary_rays(cfg: RenderCfg, sample: int = 0) -> np.ndarray:
     rays = np.empty((cfg.height * cfg.width, 6), np.float32)
     _check(lib().mcpt_primary_rays(C.byref(cfg), sample, _p(rays)))
     return rays
+
+
+def sample_batch(kind: int, u, normals, dirs=None, par0=None, par1=None, render_arithmetic: bool = False) -> np.ndarray:
+    """The device BSDF samplers (rtx.hlsl:213-302; SAMPLE_FRESNEL_TWIN: Utils.hpp:97-137) on n tuples.
+    u (n,2) uniforms used as given; render_arithmetic: the hardware-unit forms the render kernels run."""
+    c = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    normals = c(normals).reshape(-1, 3)
+    n = len(normals)
+    u = c(u)
+    if u.ndim == 1:   # fresnel draws one number
+        u = np.ascontiguousarray(np.stack([u, u], 1))
+    out = np.empty((n, 3), np.float32)
+    _check(lib().mcpt_sample_batch(kind, n, _p(u), _p(normals), _p(c(dirs)), _p(c(par0)), _p(c(par1)), int(render_arithmetic), _p(out)))
+    return out
 
 
 def counters() -> Counters:

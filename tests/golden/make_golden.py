@@ -6,6 +6,9 @@ box (no /root/reference) detect any drift of oracle, tree builder or kernels:
   golden.json   per scene: tree digest (reference-rule tree), digests of the hit records {tri, t, beta, gamma}
                 for the 512x512 un-jittered camera batch and 2^18 Philox(1) random rays, work counters, and
                 a 64x64 x 4-frame render in the reference's own RNG stream (sum digest + mean);
+  samplers_ref.npz   outputs of THE REFERENCE'S OWN samplers (CUDA/Utils.hpp:46-137 compiled on the host,
+                oracle/_ref/libmcpt_refcv.so) with the uniforms its cuRAND stream handed them: the oracle must
+                reproduce them bit for bit, the CUDA samplers to a stated bound (tests/test_samplers.py);
   hits_scene01.npz   explicit records for 128x128 camera rays + 4096 random rays (compared bit for bit with
                 the CUDA kernels in tests/test_gpu_parity.py).
 """
@@ -60,8 +63,50 @@ def scene_record(o, name):
     return rec, s, sc
 
 
+def sampler_inputs(n, seed):
+    """Unit normals / incoming directions incl. the rotation's special cases (|n.y +- 1| < FLT_EPSILON,
+    rtx.hlsl:262-267 / :287-292), near-special normals, normal and grazing incidence."""
+    g = np.random.default_rng(seed)
+    nrm = g.normal(size=(n, 3))
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    nrm = nrm.astype(np.float32)
+    nrm[0], nrm[1] = [0, 1, 0], [0, -1, 0]
+    nrm[2] = [0, np.float32(1) - np.float32(2.0 ** -24), 0]      # inside the epsilon
+    nrm[3] = [3e-4, np.sqrt(1 - 9e-8), 0]                         # just outside it
+    nrm[4] = [0, -1 + 2.0 ** -24, 1e-5]
+    nrm[5], nrm[6], nrm[7] = [1, 0, 0], [0, 0, -1], [0.6, 0.0, 0.8]
+    d = g.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d = d.astype(np.float32)
+    d[8] = -nrm[8]                                                # normal incidence
+    t = np.cross(nrm[9], [0.3, 0.5, 0.8])
+    t /= np.linalg.norm(t)
+    d[9] = (t + 1e-3 * nrm[9]).astype(np.float32)                # grazing
+    return nrm, d
+
+
+def sampler_fixture(n=8192):
+    """Runs the reference's own Utils.hpp samplers (needs oracle/_ref, i.e. /root/reference at build time)."""
+    from oracle.pyoracle import ReferenceCV
+    cv = ReferenceCV()
+    g = np.random.default_rng(21)
+    nrm, d = sampler_inputs(n, 20)
+    Ns = g.choice([2, 5, 10, 20, 50, 1000], n).astype(np.uint32)
+    Tr = g.choice([0.9, 0.5, 1.0, 0.1], n).astype(np.float32)
+    Ni = g.choice([1.5, 1.33, 2.4, 1.0], n).astype(np.float32)
+    hemi, u_hemi = cv.sample_hemi(1234, nrm)
+    phong, u_phong = cv.sample_phong(99, nrm, d, Ns)
+    fres, u_fres = cv.sample_fresnel(7, nrm, d, Tr, Ni)
+    return dict(normals=nrm, dirs=d, Ns=Ns, Tr=Tr, Ni=Ni, hemi=hemi, u_hemi=u_hemi, phong=phong, u_phong=u_phong,
+                fresnel_twin=fres, u_fresnel=u_fres)
+
+
 def main():
     o = Oracle()
+    if "--samplers" in sys.argv or not os.path.exists(os.path.join(HERE, "samplers_ref.npz")):
+        np.savez_compressed(os.path.join(HERE, "samplers_ref.npz"), **sampler_fixture())
+        if "--samplers" in sys.argv:
+            return
     out = {}
     for name in ("scene01", "scene01_lambert", "scene02", "scene03"):
         out[name], s, sc = scene_record(o, name)
