@@ -207,6 +207,13 @@ int mcpt_selfcheck_div3(int64_t n, uint32_t seed, int spread, uint64_t* mismatch
  * (gamma 2.2 = the display value of rtx.hlsl:402; 1.0 = the CUDA tracer's linear dump). */
 int mcpt_write_png(const char* path, const float* rgb, int width, int height, float gamma);
 int mcpt_write_pfm(const char* path, const float* rgb, int width, int height);
+/* ---- tuning / A-B knobs ---------------------------------------------------------------------- */
+/* The library never reads the caller's environment.  Knobs (clamped to their valid range): "shade_threshold",
+ * "cam_threshold" [1,32], "tri_cap" [1,64], "chunks" [0,64; 0 = automatic], "sah_ci", "sah_eb" [0.05,100] (next
+ * tree build), "leaf_bfs", "sah_resort", "build_timing", "sm_stats" {0,1}, "variant", "min_blocks" (MCPT_TUNE builds);
+ * "defaults" restores the shipped configuration.  None of them changes a result beyond fp32 summation order. */
+int mcpt_set_tuning(const char* name, double value);
+int mcpt_get_tuning(const char* name, double* value);
 const char* mcpt_last_error(void);
 const char* mcpt_version(void);
 

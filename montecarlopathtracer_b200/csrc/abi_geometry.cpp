@@ -22,6 +22,18 @@ int fail_cuda(cudaError_t e, const char* what) {
     return fail(MCPT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 }
 
+Tuning& tuning() {
+    static Tuning t;
+    return t;
+}
+
+int bind_device() {
+    Context& c = ctx();
+    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    const cudaError_t e = cudaSetDevice(c.device);
+    return e == cudaSuccess ? MCPT_OK : fail_cuda(e, "cudaSetDevice");
+}
+
 namespace {
 
 template <class T>
@@ -37,17 +49,29 @@ void release_device_scene(Context& c) {
     c.uploaded = false;
 }
 
+// Builds tree and device tables into locals and commits them to the context only when all of it succeeded: a
+// failed call leaves the previous geometry (host tables, tree AND device tables) exactly as it was.  If the upload
+// of a committed scene fails, the context holds the new host tables with nothing on the device (uploaded = false;
+// the next device call retries the upload) -- never a mix of new host tables and old device tables.
 int install_scene(HostScene&& scene, int build_mode) {
     Context& c = ctx();
     std::string err;
     if (build_mode != MCPT_BUILD_REFERENCE && build_mode != MCPT_BUILD_SAH) return fail(MCPT_ERR_INVALID, "unknown build_mode");
     if (!validate_scene(scene, err)) return fail(MCPT_ERR_INVALID, err);
+    HostTree tree;
+    PackedScene packed;
+    build_kd_tree(scene, build_mode, tree);
+    if (!pack_scene(scene, tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
     c.scene = std::move(scene);
-    build_kd_tree(c.scene, build_mode, c.tree);
-    if (!pack_scene(c.scene, c.tree, c.packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
+    c.tree = std::move(tree);
+    c.packed = std::move(packed);
     c.has_geometry = true;
     c.uploaded = false;
-    if (c.has_device) return ensure_uploaded();
+    if (c.has_device) {
+        const int rc = ensure_uploaded();
+        if (rc != MCPT_OK) { cudaSetDevice(c.device); release_device_scene(c); }
+        return rc;
+    }
     return MCPT_OK;
 }
 
@@ -56,7 +80,7 @@ int install_scene(HostScene&& scene, int build_mode) {
 // Host tables -> HBM.  One H2D copy per table on the context stream.
 int ensure_uploaded() {
     Context& c = ctx();
-    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    if (const int rc = bind_device()) return rc;
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry: call mcpt_create_geometry / mcpt_load_obj first");
     if (c.uploaded) return MCPT_OK;
     cudaError_t e;
@@ -91,6 +115,7 @@ using namespace mcpt;
 extern "C" {
 
 int mcpt_initialize(int device) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     int n = 0;
@@ -111,9 +136,11 @@ int mcpt_initialize(int device) {
     c.device = device;
     if (c.has_geometry) return ensure_uploaded();
     return MCPT_OK;
+    });
 }
 
 int mcpt_shutdown(void) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (c.has_device) {
@@ -131,9 +158,11 @@ int mcpt_shutdown(void) {
     c.has_geometry = false;
     c.scene = HostScene(); c.tree = HostTree(); c.packed = PackedScene();
     return MCPT_OK;
+    });
 }
 
 int mcpt_create_geometry(const mcpt_scene_desc* d) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!d || !d->vertices || !d->triangles || !d->materials || d->num_vertices <= 0 || d->num_triangles <= 0 ||
@@ -145,9 +174,11 @@ int mcpt_create_geometry(const mcpt_scene_desc* d) {
     s.triangles.assign(d->triangles, d->triangles + 7 * static_cast<size_t>(d->num_triangles));
     s.materials.assign(d->materials, d->materials + 12 * static_cast<size_t>(d->num_materials));
     return install_scene(std::move(s), d->build_mode);
+    });
 }
 
 int mcpt_load_obj(const char* obj_path, const char* mtl_base, int loader, int build_mode) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!obj_path) return fail(MCPT_ERR_INVALID, "mcpt_load_obj: null path");
@@ -155,9 +186,11 @@ int mcpt_load_obj(const char* obj_path, const char* mtl_base, int loader, int bu
     std::string err;
     if (!load_obj_scene(obj_path, mtl_base ? mtl_base : "", loader, s, err)) return fail(MCPT_ERR_IO, err);
     return install_scene(std::move(s), build_mode);
+    });
 }
 
 int mcpt_load_scene_file(const char* path, int build_mode) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!path) return fail(MCPT_ERR_INVALID, "mcpt_load_scene_file: null path");
@@ -165,27 +198,33 @@ int mcpt_load_scene_file(const char* path, int build_mode) {
     std::string err;
     if (!load_scene_file(path, s, err)) return fail(MCPT_ERR_IO, err);
     return install_scene(std::move(s), build_mode);
+    });
 }
 
 int mcpt_destroy_geometry(void) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (c.has_device) { cudaSetDevice(c.device); release_device_scene(c); }
     c.has_geometry = false;
     c.scene = HostScene(); c.tree = HostTree(); c.packed = PackedScene();
     return MCPT_OK;
+    });
 }
 
 int mcpt_check_stackless_layout(void) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
     std::string err;
     if (!check_ropes(c.tree, c.packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
     return MCPT_OK;
+    });
 }
 
 int mcpt_get_tree_info(mcpt_tree_info* info) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!info) return fail(MCPT_ERR_INVALID, "null info");
@@ -198,10 +237,12 @@ int mcpt_get_tree_info(mcpt_tree_info* info) {
     info->build_seconds = c.tree.build_seconds;
     info->device_bytes = c.packed.bytes();
     return MCPT_OK;
+    });
 }
 
 int mcpt_get_tree(uint32_t* left, uint32_t* right, float* aabb6, uint32_t* split_axis, float* split_value,
                   uint32_t* leaf_offset, uint32_t* leaf_count, uint32_t* leaf_ids) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
@@ -216,9 +257,11 @@ int mcpt_get_tree(uint32_t* left, uint32_t* right, float* aabb6, uint32_t* split
     if (leaf_count) std::memcpy(leaf_count, t.leaf_count.data(), n * 4);
     if (leaf_ids) std::memcpy(leaf_ids, t.leaf_ids.data(), t.leaf_ids.size() * 4);
     return MCPT_OK;
+    });
 }
 
 int mcpt_get_scene(int32_t counts[4], float* vertices, float* normals, uint32_t* triangles, float* materials) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
@@ -232,6 +275,59 @@ int mcpt_get_scene(int32_t counts[4], float* vertices, float* normals, uint32_t*
     if (triangles) std::memcpy(triangles, s.triangles.data(), s.triangles.size() * 4);
     if (materials) std::memcpy(materials, s.materials.data(), s.materials.size() * 4);
     return MCPT_OK;
+    });
+}
+
+int mcpt_set_tuning(const char* name, double value) {
+    return guarded([&]() -> int {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!name) return fail(MCPT_ERR_INVALID, "null tuning name");
+    Tuning& t = tuning();
+    const std::string k(name);
+    auto clampi = [&](int lo, int hi) { return static_cast<int>(value < lo ? lo : (value > hi ? hi : value)); };
+    auto clampf = [&](float lo, float hi) { return static_cast<float>(value < lo ? lo : (value > hi ? hi : value)); };
+    if (!(value == value)) return fail(MCPT_ERR_INVALID, "tuning value is NaN");
+    if (k == "shade_threshold") t.shade_threshold = clampi(1, 32);
+    else if (k == "cam_threshold") t.cam_threshold = clampi(1, 32);
+    else if (k == "tri_cap") t.tri_cap = clampi(1, 64);
+    else if (k == "chunks") t.chunks = clampi(0, 64);
+    else if (k == "min_blocks") t.min_blocks = clampi(1, 16);
+    else if (k == "variant") t.variant = clampi(0, 4095);
+    else if (k == "leaf_bfs") t.leaf_bfs = clampi(0, 1);
+    else if (k == "sah_resort") t.sah_resort = clampi(0, 1);
+    else if (k == "build_timing") t.build_timing = clampi(0, 1);
+    else if (k == "sm_stats") t.sm_stats = clampi(0, 1);
+    else if (k == "sah_ci") t.sah_ci = clampf(0.05f, 100.0f);
+    else if (k == "sah_eb") t.sah_eb = clampf(0.05f, 100.0f);
+    else if (k == "defaults") t = Tuning();
+    else return fail(MCPT_ERR_INVALID, "unknown tuning knob: " + k);
+    return MCPT_OK;
+    });
+}
+
+int mcpt_get_tuning(const char* name, double* value) {
+    return guarded([&]() -> int {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!name || !value) return fail(MCPT_ERR_INVALID, "null argument");
+    const Tuning& t = tuning();
+    const std::string k(name);
+    if (k == "shade_threshold") *value = t.shade_threshold;
+    else if (k == "cam_threshold") *value = t.cam_threshold;
+    else if (k == "tri_cap") *value = t.tri_cap;
+    else if (k == "chunks") *value = t.chunks;
+    else if (k == "min_blocks") *value = t.min_blocks;
+    else if (k == "variant") *value = t.variant;
+    else if (k == "leaf_bfs") *value = t.leaf_bfs;
+    else if (k == "sah_resort") *value = t.sah_resort;
+    else if (k == "build_timing") *value = t.build_timing;
+    else if (k == "sm_stats") *value = t.sm_stats;
+    else if (k == "sah_ci") *value = t.sah_ci;
+    else if (k == "sah_eb") *value = t.sah_eb;
+    else return fail(MCPT_ERR_INVALID, "unknown tuning knob: " + k);
+    return MCPT_OK;
+    });
 }
 
 const char* mcpt_last_error(void) { return ctx().last_error.c_str(); }

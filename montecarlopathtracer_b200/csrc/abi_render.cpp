@@ -14,11 +14,6 @@ using namespace mcpt;
 
 namespace {
 
-int env_int(const char* name, int dflt) {
-    const char* v = std::getenv(name);
-    return v && *v ? std::atoi(v) : dflt;
-}
-
 // How many slices the spp of a pixel are cut into (grid.z; each slice accumulates into its own buffer, one
 // reduce pass adds them).  Two reasons to cut: (1) small images: enough threads to fill 148 SMs several times
 // over; (2) the tail: a block carries all the samples of its 16x16 tile, the 4 096 blocks of a 1024^2 image
@@ -34,7 +29,7 @@ int pick_chunks(int width, int height, int spp) {
     chunks = std::max(chunks, forTail);
     chunks = std::max(1LL, std::min<long long>(chunks, spp));
     chunks = std::min<long long>(chunks, 64);
-    const int forced = env_int("MCPT_CHUNKS", 0);  // tuning knob
+    const int forced = tuning().chunks;  // mcpt_set_tuning("chunks", n): tests (slice independence) and tuning
     if (forced > 0) chunks = std::min(forced, spp);
     return static_cast<int>(chunks);
 }
@@ -95,11 +90,14 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.nee = (cfg->flags & MCPT_FLAG_NEE) != 0;
     r.moments = moments;
     r.state_machine = (cfg->flags & MCPT_FLAG_SIMPLE_KERNEL) == 0;
-    r.shade_threshold = env_int("MCPT_SM_SHADE", 18);      // tuning knobs, defaults from profiles/r1_tuning.md
-    r.min_blocks = env_int("MCPT_SM_MINBLOCKS", 4);
-    r.variant = env_int("MCPT_SM_VARIANT", 503);
-    r.cam_threshold = env_int("MCPT_SM_CAMR", 16);
-    r.tri_cap = std::max(1, env_int("MCPT_SM_TRICAP", 4));
+    // Knobs come from mcpt_set_tuning only (never the environment) and are clamped there AND here: a vote threshold
+    // above the warp size could never be met and render_kernel_sm would spin for ever.
+    const Tuning& tn = tuning();
+    r.shade_threshold = std::min(32, std::max(1, tn.shade_threshold));
+    r.cam_threshold = std::min(32, std::max(1, tn.cam_threshold));
+    r.tri_cap = std::min(64, std::max(1, tn.tri_cap));
+    r.min_blocks = tn.min_blocks;   // MCPT_TUNE builds only
+    r.variant = tn.variant;         // MCPT_TUNE builds only
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
         // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))
         // per frame, i.e. the raw generator output.
@@ -154,13 +152,14 @@ int finish_counters(cudaStream_t stream) {
     cudaEventElapsedTime(&t, c.ev[0], c.ev[2]);
     const unsigned long long rays = cnt[0];
     c.counters.rays = rays;
-    if (cnt[1] && std::getenv("MCPT_SM_STATS")) {  // tuning builds, VAR bit 3
+    if (cnt[1] && tuning().sm_stats) {  // tuning builds, VAR bit 3
         std::fprintf(stderr, "rounds %llu lanes/round %.2f | node steps: mean/lane %.2f max %.2f | tri tests: mean/lane %.2f max %.2f | shade phases %llu lanes/phase %.2f done/phase %.2f | rounds/phase %.2f | raw3 %llu raw4 %llu\n",
                      cnt[1], double(cnt[2]) / cnt[1], double(cnt[3]) / cnt[2], double(cnt[4]) / cnt[1], double(cnt[5]) / cnt[2], double(cnt[6]) / cnt[1],
                      cnt[7], double(cnt[8]) / cnt[7], double(cnt[9]) / cnt[7], double(cnt[1]) / cnt[7], cnt[3], cnt[4]);
     }
     c.counters.kernel_ms = k;
     c.counters.total_ms = t;
+    if (cnt[15]) return fail(MCPT_ERR_INTERNAL, "stackless traversal exceeded its hop budget (inconsistent neighbour links?): the affected rays were ended as misses");
     return MCPT_OK;
 }
 
@@ -191,6 +190,7 @@ void mcpt_cuda_twin_render_cfg(mcpt_render_cfg* cfg, int width, int height, int 
 }
 
 int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m2) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!host_rgb) return fail(MCPT_ERR_INVALID, "null host_rgb");
@@ -209,9 +209,11 @@ int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m
         if ((e = cudaMemcpyAsync(host_m2, c.d_rgb.ptr, 3 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H m2");
     }
     return finish_counters(c.stream);
+    });
 }
 
 int mcpt_render_accumulate_device(const mcpt_render_cfg* cfg, void* dev_sum, void* dev_sumsq, void* stream) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!dev_sum) return fail(MCPT_ERR_INVALID, "null dev_sum");
@@ -219,10 +221,12 @@ int mcpt_render_accumulate_device(const mcpt_render_cfg* cfg, void* dev_sum, voi
     int rc = render_core(cfg, s, static_cast<float4*>(dev_sum), static_cast<float4*>(dev_sumsq), nullptr, nullptr);
     if (rc) return rc;
     return finish_counters(s);
+    });
 }
 
 int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, void* dev_tri, void* dev_t,
                                 void* dev_beta, void* dev_gamma, void* stream) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (n < 0 || (n > 0 && (!dev_rays || !dev_tri))) return fail(MCPT_ERR_INVALID, "bad ray batch");
@@ -242,9 +246,11 @@ int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, vo
     cudaEventElapsedTime(&k, c.ev[0], c.ev[1]);
     c.counters.paths = 0; c.counters.rays = static_cast<uint64_t>(n); c.counters.kernel_ms = k; c.counters.total_ms = k;
     return MCPT_OK;
+    });
 }
 
 int mcpt_intersect_batch(const float* rays, int64_t n, int variant, int32_t* tri, float* t, float* beta, float* gamma) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     {
         std::lock_guard<std::mutex> g(c.lock);
@@ -269,15 +275,17 @@ int mcpt_intersect_batch(const float* rays, int64_t n, int variant, int32_t* tri
     if (e == cudaSuccess && gamma) e = cudaMemcpy(gamma, c.d_gamma.ptr, N * 4, cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) return fail_cuda(e, "D2H hits");
     return MCPT_OK;
+    });
 }
 
 int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     int rc = check_cfg(cfg);
     if (rc) return rc;
     if (!host_rays || sample < 0) return fail(MCPT_ERR_INVALID, "bad arguments");
-    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    if (const int brc = bind_device()) return brc;
     const size_t pixels = static_cast<size_t>(cfg->width) * cfg->height;
     cudaError_t e;
     if ((e = c.d_rays.ensure(6 * pixels)) != cudaSuccess) return fail_cuda(e, "alloc rays");
@@ -296,10 +304,12 @@ int mcpt_primary_rays(const mcpt_render_cfg* cfg, int sample, float* host_rays) 
     if ((e = cudaMemcpyAsync(host_rays, c.d_rays.ptr, 6 * pixels * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H rays");
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "primary rays");
     return MCPT_OK;
+    });
 }
 
 int mcpt_sample_batch(int kind, int64_t n, const float* u, const float* normals, const float* dirs, const float* par0,
                       const float* par1, int render_arithmetic, float* out) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (kind < MCPT_SAMPLE_HEMI || kind > MCPT_SAMPLE_FRESNEL_TWIN) return fail(MCPT_ERR_INVALID, "unknown sampler kind");
@@ -307,7 +317,7 @@ int mcpt_sample_batch(int kind, int64_t n, const float* u, const float* normals,
     if (n > 0 && kind != MCPT_SAMPLE_HEMI && !dirs) return fail(MCPT_ERR_INVALID, "this sampler needs incoming directions");
     if (n > 0 && kind != MCPT_SAMPLE_HEMI && !par0) return fail(MCPT_ERR_INVALID, "missing sampler parameter (Ns / Tr)");
     if (n > 0 && kind >= MCPT_SAMPLE_FRESNEL && !par1) return fail(MCPT_ERR_INVALID, "missing sampler parameter (Ni)");
-    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    if (const int brc = bind_device()) return brc;
     if (n == 0) return MCPT_OK;
     const size_t N = static_cast<size_t>(n);
     // one scratch buffer: u (2N) | normals (3N) | dirs (3N) | par0 (N) | par1 (N) | out (3N)
@@ -327,9 +337,11 @@ int mcpt_sample_batch(int kind, int64_t n, const float* u, const float* normals,
     if ((e = cudaMemcpyAsync(out, dout, 3 * N * sizeof(float), cudaMemcpyDeviceToHost, c.stream)) != cudaSuccess) return fail_cuda(e, "D2H");
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "sampler batch");
     return MCPT_OK;
+    });
 }
 
 int mcpt_traversal_stats(const float* rays, int64_t n, int variant, uint64_t out[3]) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (n <= 0 || !rays || !out) return fail(MCPT_ERR_INVALID, "bad ray batch");
@@ -346,13 +358,15 @@ int mcpt_traversal_stats(const float* rays, int64_t n, int variant, uint64_t out
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "tally");
     out[0] = h[0]; out[1] = h[1]; out[2] = h[2];
     return MCPT_OK;
+    });
 }
 
 int mcpt_measure_fp32_peak(double* gflops) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!gflops) return fail(MCPT_ERR_INVALID, "null gflops");
-    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    if (const int brc = bind_device()) return brc;
     const int blocks = 148 * 16, iters = 1 << 14;
     cudaError_t e;
     if ((e = c.d_rgb.ensure(static_cast<size_t>(blocks) * 256)) != cudaSuccess) return fail_cuda(e, "alloc");
@@ -368,13 +382,15 @@ int mcpt_measure_fp32_peak(double* gflops) {
     }
     *gflops = best;
     return MCPT_OK;
+    });
 }
 
 int mcpt_selfcheck_div3(int64_t n, uint32_t seed, int spread, uint64_t* mismatches, uint64_t* fast_path) {
+    return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!mismatches || !fast_path || n < 0 || spread < 0 || spread > 126) return fail(MCPT_ERR_INVALID, "bad self-check arguments");
-    if (!c.has_device) return fail(MCPT_ERR_NO_DEVICE, "mcpt_initialize has not bound a CUDA device; libmcpt has no CPU path");
+    if (const int brc = bind_device()) return brc;
     cudaError_t e;
     if ((e = c.d_counter.ensure(16)) != cudaSuccess) return fail_cuda(e, "alloc counters");
     if ((e = cudaMemsetAsync(c.d_counter.ptr, 0, 16 * sizeof(unsigned long long), c.stream)) != cudaSuccess) return fail_cuda(e, "memset");
@@ -384,12 +400,15 @@ int mcpt_selfcheck_div3(int64_t n, uint32_t seed, int spread, uint64_t* mismatch
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "self-check");
     *mismatches = h[0]; *fast_path = h[1];
     return MCPT_OK;
+    });
 }
 
 int mcpt_get_counters(mcpt_counters* out) {
+    return guarded([&]() -> int {
     if (!out) return fail(MCPT_ERR_INVALID, "null counters");
     *out = ctx().counters;
     return MCPT_OK;
+    });
 }
 
 }  // extern "C"

@@ -72,6 +72,11 @@ int main(int argc, char** argv) {
                  scene.c_str(), ti.num_nodes, ti.num_leaves, ti.num_leaf_refs, ti.max_depth, ti.num_emitter_triangles, ti.build_seconds,
                  ti.device_bytes / 1048576.0);
 
+    // same limits as mcpt_render_scene's check_cfg, applied BEFORE anything is sized from the command line
+    if (cfg.width <= 0 || cfg.height <= 0 || cfg.width > 32768 || cfg.height > 32768 || cfg.spp <= 0) {
+        std::fprintf(stderr, "mcpt_cli: --w/--h must be in 1..32768 and --spp positive\n");
+        return 2;
+    }
     const size_t pixels = static_cast<size_t>(cfg.width) * cfg.height;
     std::vector<float> img(3 * pixels, 0.0f), part(3 * pixels);
     const int total = cfg.spp;

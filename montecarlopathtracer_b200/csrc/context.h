@@ -3,7 +3,9 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <exception>
 #include <mutex>
+#include <new>
 #include <string>
 
 #include "../../include/mcpt.h"
@@ -62,6 +64,22 @@ struct Context {
 Context& ctx();
 int fail(int code, const std::string& msg);
 int fail_cuda(cudaError_t e, const char* what);
-int ensure_uploaded();  // needs lock held
+int ensure_uploaded();  // needs lock held; binds the context's device to the calling thread
+int bind_device();      // cudaSetDevice(context device): the current device is per host thread, so every entry point
+                        // that touches the device calls this first (MCPT_ERR_NO_DEVICE when none is bound)
+
+// No exception crosses the C boundary (include/mcpt.h): every extern "C" body runs inside guarded().
+template <class F>
+int guarded(F&& body) noexcept {
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        return fail(MCPT_ERR_INTERNAL, "out of host memory");
+    } catch (const std::exception& e) {
+        try { return fail(MCPT_ERR_INTERNAL, std::string("exception: ") + e.what()); } catch (...) { return MCPT_ERR_INTERNAL; }
+    } catch (...) {
+        try { return fail(MCPT_ERR_INTERNAL, "unknown exception"); } catch (...) { return MCPT_ERR_INTERNAL; }
+    }
+}
 
 }  // namespace mcpt

@@ -26,8 +26,7 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     {
         std::vector<uint32_t> todo(1, 0u);
         uint32_t ordinal = 0;
-        const char* bfs = std::getenv("MCPT_LEAF_BFS");  // A/B knob: keep the breadth-first leaf order
-        if (bfs && *bfs == '1') {
+        if (tuning().leaf_bfs) {  // A/B knob: keep the breadth-first leaf order
             todo.clear();
             for (uint32_t k = 0; k < nN; ++k)
                 if (tree.split_axis[k] == 0) {

@@ -36,6 +36,25 @@ struct HostTree {
     size_t num_nodes() const { return left.size(); }
 };
 
+// Tuning and A/B knobs.  The library never reads the caller's environment: the only way to change them is
+// mcpt_set_tuning() (values clamped), which the test and tuning scripts call explicitly.  Defaults = shipped
+// configuration (profiles/r1_tuning.md, profiles/r2_tuning.md).
+struct Tuning {
+    int shade_threshold = 18;  // lanes that must have finished rays before a warp leaves TRAVERSE     [1, 32]
+    int cam_threshold = 16;    // lanes that must need a camera ray before the warp refills its queue  [1, 32]
+    int tri_cap = 4;           // triangle tests per lane and round                                    [1, 64]
+    int chunks = 0;            // sample slices per tile, 0 = pick_chunks' choice                      [0, 64]
+    int min_blocks = 4;        // MCPT_TUNE builds only: resident blocks per SM
+    int variant = 503;         // MCPT_TUNE builds only: VAR bits of render_kernel_sm
+    int leaf_bfs = 0;          // A/B: breadth-first instead of depth-first device order of the leaves
+    int sah_resort = 0;        // A/B: the re-sorting SAH builder on every level
+    int build_timing = 0;      // print builder phase timings to stderr
+    int sm_stats = 0;          // MCPT_TUNE builds, VAR bit 3: print per-warp round statistics
+    float sah_ci = 1.0f;       // SAH: cost of a triangle test relative to a node step              [0.05, 100]
+    float sah_eb = 1.0f;       // SAH: multiplier when one child is empty                            [0.05, 100]
+};
+Tuning& tuning();
+
 // kd_build.cpp
 // mode 0: node-for-node the tree of KDTree.hpp:58-287; mode 1: own SAH builder.
 void build_kd_tree(const HostScene& scene, int mode, HostTree& out);

@@ -46,6 +46,7 @@ void chunk(std::vector<uint8_t>& out, const char type[4], const std::vector<uint
 extern "C" {
 
 int mcpt_write_png(const char* path, const float* rgb, int width, int height, float gamma) {
+    return mcpt::guarded([&]() -> int {
     if (!path || !rgb || width <= 0 || height <= 0 || !(gamma > 0)) return mcpt::fail(MCPT_ERR_INVALID, "mcpt_write_png: bad arguments");
     const size_t stride = 1 + 3 * static_cast<size_t>(width);
     std::vector<uint8_t> raw(stride * static_cast<size_t>(height));
@@ -84,9 +85,11 @@ int mcpt_write_png(const char* path, const float* rgb, int width, int height, fl
     const bool ok = std::fwrite(out.data(), 1, out.size(), f) == out.size();
     std::fclose(f);
     return ok ? MCPT_OK : mcpt::fail(MCPT_ERR_IO, std::string("short write to ") + path);
+    });
 }
 
 int mcpt_write_pfm(const char* path, const float* rgb, int width, int height) {
+    return mcpt::guarded([&]() -> int {
     if (!path || !rgb || width <= 0 || height <= 0) return mcpt::fail(MCPT_ERR_INVALID, "mcpt_write_pfm: bad arguments");
     FILE* f = std::fopen(path, "wb");
     if (!f) return mcpt::fail(MCPT_ERR_IO, std::string("cannot write ") + path);
@@ -96,6 +99,7 @@ int mcpt_write_pfm(const char* path, const float* rgb, int width, int height) {
         ok = std::fwrite(rgb + static_cast<size_t>(y) * 3 * width, sizeof(float), 3 * static_cast<size_t>(width), f) == 3 * static_cast<size_t>(width);
     std::fclose(f);
     return ok ? MCPT_OK : mcpt::fail(MCPT_ERR_IO, std::string("short write to ") + path);
+    });
 }
 
 }  // extern "C"

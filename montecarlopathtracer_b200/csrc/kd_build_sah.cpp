@@ -43,14 +43,11 @@ struct Node {
     std::vector<uint32_t> ids;
 };
 
-float env_float(const char* name, float dflt) {
-    const char* v = std::getenv(name);
-    return v && *v ? static_cast<float>(std::atof(v)) : dflt;
-}
 const float kTraversalCost = 1.0f;
-// the strict Cramer test + its loads against one plane step; defaults from profiles/r1_tuning.md
-const float kIntersectCost = env_float("MCPT_SAH_CI", 1.0f);
-const float kEmptyBonus = env_float("MCPT_SAH_EB", 1.0f);
+// the strict Cramer test + its loads against one plane step; defaults from profiles/r1_tuning.md.  Read once per
+// build from tuning() (mcpt_set_tuning), never from the environment.
+float kIntersectCost = 1.0f;
+float kEmptyBonus = 1.0f;
 
 inline float surface(const Box& b) {
     const float x = b.hi[0] - b.lo[0], y = b.hi[1] - b.lo[1], z = b.hi[2] - b.lo[2];
@@ -458,6 +455,8 @@ void build_node_sorted(const HostScene& s, std::vector<Node>& nodes, int me, std
 }  // namespace
 
 void build_sah_tree(const HostScene& scene, HostTree& out) {
+    kIntersectCost = tuning().sah_ci;
+    kEmptyBonus = tuning().sah_eb;
     auto t0 = std::chrono::steady_clock::now();
     const size_t nT = scene.num_triangles();
     std::vector<Ref> refs(nT);
@@ -478,8 +477,7 @@ void build_sah_tree(const HostScene& scene, HostTree& out) {
     nodes.reserve(6 * nT + 1024);
     nodes.emplace_back();
     nodes[0].cell = root;
-    const char* resort = std::getenv("MCPT_SAH_RESORT");  // A/B knob: the re-sorting builder on every level
-    if (resort && *resort == '1') {
+    if (tuning().sah_resort) {  // A/B knob: the re-sorting builder on every level
 #pragma omp parallel
 #pragma omp single
         build_node(scene, nodes, 0, refs, 0, maxDepth);
@@ -501,7 +499,7 @@ void build_sah_tree(const HostScene& scene, HostTree& out) {
             build_node_sorted(scene, nodes, 0, refs, ev, 0, maxDepth);
         }
     }
-    if (std::getenv("MCPT_BUILD_TIMING")) std::fprintf(stderr, "sah: recursion %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+    if (tuning().build_timing) std::fprintf(stderr, "sah: recursion %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
 
     // breadth-first renumbering, children adjacent (same layout as the reference flatten)
     std::vector<int> order;
@@ -550,7 +548,7 @@ void build_sah_tree(const HostScene& scene, HostTree& out) {
             std::copy(n.ids.begin(), n.ids.end(), out.leaf_ids.begin() + out.leaf_offset[k]);
         }
     }
-    if (std::getenv("MCPT_BUILD_TIMING")) std::fprintf(stderr, "sah: recursion + flatten %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+    if (tuning().build_timing) std::fprintf(stderr, "sah: recursion + flatten %.3f s\n", std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
     out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
 

@@ -1,7 +1,7 @@
 // Path-sampling kernel, persistent-lane variant (the render path).
 //
 // ncu on the first kernel (render.cuh: one whole ray per loop iteration) showed 4.9 of 32 lanes
-// active per issued instruction (profiles/r1a_*): incoherent bounce rays need very different numbers
+// active per issued instruction (profiles/r1_tuning.md): incoherent bounce rays need very different numbers
 // of node steps and leaf visits, and at every trace call the warp waited for its slowest lane.
 // Here a lane keeps its traversal state (node, interval, stack, closest hit) in registers ACROSS
 // loop iterations and the warp alternates two phases:
@@ -224,6 +224,13 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         start_sample(); begin_ray();
     }
 
+    // Hop budget in warp-uniform form (ballot results live in uniform registers; a per-lane hop counter would cost a
+    // register this kernel does not have): `stall` counts consecutive TRAVERSE rounds in which the set of waiting lanes
+    // did not change, i.e. in which NO lane of the warp finished a ray.  MCPT_ROPE_MAX_HOPS such rounds mean every ray
+    // in flight has made that many hops without ending -- impossible with consistent tables (each hop moves monotonically
+    // along the ray's axes) -- so the rays are ended as misses and the host call reports MCPT_ERR_INTERNAL.
+    uint32_t prevWaiting = 0u, stall = 0u;
+
     while (true) {
         {
             // ================= SHADE: consume the hit, produce the next ray ====================
@@ -362,7 +369,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                     const float4 h0 = ldg4(p.sc.leaf_blob + off), h1 = ldg4(p.sc.leaf_blob + off + 1);
                     const LeafExit e = leaf_exit(p.sc, off, h0, h1, ox, oy, oz, ix, iy, iz, nearBits);
                     // No hop counter here (it costs a register the kernel does not have; intersect_ropes keeps one):
-                    // the walk terminates structurally.  The face taken on each axis is fixed by the ray's sign bits,
+                    // the walk terminates structurally -- GIVEN consistent tables (kd_ropes.cpp builds them; check_ropes,
+                    // exposed as mcpt_check_stackless_layout, verifies them for every scene and builder in the CPU suite).
+                    // A warp-level budget of TRAVERSE rounds (`roundsLeft`, below) bounds the kernel regardless.  The face taken on each axis is fixed by the ray's sign bits,
                     // a rope's subtree lies wholly beyond that face, so the cell's bound on the exit axis moves
                     // strictly in the sign direction every hop whatever the float values (NaN included) and the
                     // number of hops is bounded by the number of split planes.
@@ -390,7 +399,18 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                 st[3] += __reduce_add_sync(0xFFFFFFFFu, myNodes); st[4] += __reduce_max_sync(0xFFFFFFFFu, myNodes);
                 st[5] += __reduce_add_sync(0xFFFFFFFFu, myTris); st[6] += __reduce_max_sync(0xFFFFFFFFu, myTris);
             }
-            if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER && state != ST_LEAF)) >= shadeThreshold) break;
+            const uint32_t waiting = __ballot_sync(0xFFFFFFFFu, state != ST_INNER && state != ST_LEAF);
+            if (ROPES) {
+                if (waiting != prevWaiting) {
+                    prevWaiting = waiting; stall = 0u;
+                } else if (++stall > MCPT_ROPE_MAX_HOPS) {
+                    if (state == ST_INNER || state == ST_LEAF) { htri = 0xFFFFFFFFu; state = ST_SHADE; }
+                    if ((threadIdx.x & 31u) == 0u) atomicExch(p.ray_counter + 15, 1ull);
+                    stall = 0u;
+                    break;
+                }
+            }
+            if (__popc(waiting) >= shadeThreshold) break;
         }
     }
 

@@ -44,6 +44,21 @@ bool load_scene_file(const std::string& path, HostScene& out, std::string& err) 
     char magic[8];
     uint32_t n[4];
     bool ok = fread(magic, 1, 8, f) == 8 && memcmp(magic, kMagic, 8) == 0 && fread(n, 4, 4, f) == 4;
+    if (ok) {
+        // The counts come from an untrusted file: they must fit the ABI's int32 counts and add up to exactly the
+        // bytes that follow the header, BEFORE anything is sized from them.
+        long here = ftell(f);
+        ok = here >= 0 && fseek(f, 0, SEEK_END) == 0;
+        const long end = ok ? ftell(f) : -1;
+        ok = ok && end >= here && fseek(f, here, SEEK_SET) == 0;
+        const unsigned long long need = 4ull * (3ull * n[0] + 3ull * n[1] + 7ull * n[2] + 12ull * n[3]);
+        if (ok && (n[0] > 0x7FFFFFFFu || n[1] > 0x7FFFFFFFu || n[2] > 0x7FFFFFFFu || n[3] > 0x7FFFFFFFu ||
+                   need != static_cast<unsigned long long>(end - here))) {
+            fclose(f);
+            err = path + ": header counts do not match the file size";
+            return false;
+        }
+    }
     ok = ok && read_vec(f, out.vertices, 3 * static_cast<size_t>(n[0])) && read_vec(f, out.normals, 3 * static_cast<size_t>(n[1])) &&
          read_vec(f, out.triangles, 7 * static_cast<size_t>(n[2])) && read_vec(f, out.materials, 12 * static_cast<size_t>(n[3]));
     fclose(f);

@@ -97,6 +97,8 @@ def lib() -> C.CDLL:
     L.mcpt_selfcheck_div3.argtypes = [C.c_int64, C.c_uint32, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.mcpt_write_png.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int, C.c_float]
     L.mcpt_write_pfm.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
+    L.mcpt_set_tuning.argtypes = [C.c_char_p, C.c_double]
+    L.mcpt_get_tuning.argtypes = [C.c_char_p, C.POINTER(C.c_double)]
     L.mcpt_last_error.restype = C.c_char_p
     L.mcpt_version.restype = C.c_char_p
     _lib = L
@@ -315,6 +317,35 @@ def write_pfm(path: str, rgb: np.ndarray) -> None:
     rgb = np.ascontiguousarray(rgb, np.float32)
     h, w, _ = rgb.shape
     _check(lib().mcpt_write_pfm(path.encode(), _p(rgb), w, h))
+
+
+def set_tuning(name: str, value: float) -> None:
+    """A/B and tuning knobs of include/mcpt.h (clamped by the library; "defaults" restores the shipped values).  The
+    library never reads the environment: scripts that sweep knobs call this explicitly."""
+    _check(lib().mcpt_set_tuning(name.encode(), float(value)))
+
+
+def get_tuning(name: str) -> float:
+    v = C.c_double()
+    _check(lib().mcpt_get_tuning(name.encode(), C.byref(v)))
+    return v.value
+
+
+_ENV_KNOBS = {"MCPT_SM_SHADE": "shade_threshold", "MCPT_SM_CAMR": "cam_threshold", "MCPT_SM_TRICAP": "tri_cap", "MCPT_CHUNKS": "chunks",
+              "MCPT_SM_MINBLOCKS": "min_blocks", "MCPT_SM_VARIANT": "variant", "MCPT_SAH_CI": "sah_ci", "MCPT_SAH_EB": "sah_eb",
+              "MCPT_LEAF_BFS": "leaf_bfs", "MCPT_SAH_RESORT": "sah_resort", "MCPT_BUILD_TIMING": "build_timing", "MCPT_SM_STATS": "sm_stats"}
+
+
+def tuning_from_env() -> dict:
+    """For the sweep scripts under tools/: forwards the round-1 MCPT_* environment knobs to set_tuning.  Called by
+    those scripts only -- never by the library, the tests or the default bench."""
+    applied = {}
+    for env, knob in _ENV_KNOBS.items():
+        v = os.environ.get(env)
+        if v:
+            set_tuning(knob, float(v))
+            applied[knob] = get_tuning(knob)
+    return applied
 
 
 def version() -> str:

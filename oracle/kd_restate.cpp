@@ -5,7 +5,7 @@
 //   MCRT/QuinEngine/Utils/Structure.hpp:91-183   (QuinAABB / QuinTriangle arithmetic)
 //   MCRT/QuinEngine/RTX/ShaderResource.hpp:128-179 (BFS flatten, children adjacent)
 // It is pinned node-for-node (topology, boxes, split planes, leaf id lists) against the
-// reference's own code compiled in oracle/_ref (tests/test_oracle_tree.py).
+// reference's own code compiled in oracle/_ref (tests/test_oracle_pins.py::test_restated_builder_equals_reference_builder).
 // Compile with -ffp-contract=off: every float expression below keeps the reference's
 // operand order, and must round the way the reference's x86 build does.
 #include <algorithm>

@@ -1,0 +1,221 @@
+"""BASELINE.json's configurations at THEIR OWN SIZE against the reference render (the oracle in the reference's
+own random stream), north_star's wording: "per-pixel radiance within tolerance of the reference render at matched
+spp: mean relative error < 1 %, no pixel beyond 4 sigma of its sample variance".
+
+  K1  512^2 x 16 spp, depth 5      oracle run live (4.2 M paths, about a second), GPU in MCPT_RNG_REFERENCE: the same
+                                   sample stream, pixel for pixel;
+  K2  1024^2 x 1024 spp, depth 8   frozen matched-spp oracle renders (tests/golden/fullsize_*.npz, made by
+  K3a 1024^2 x 2048 spp (scene01)  tests/golden/make_fullsize.py: per-pixel mean + sigma on a pixel lattice, 4x4 tile
+  K3b 1024^2 x 2048 spp (scene02)  means of the whole image), compared twice: with the GPU on the reference's own
+  S3  512^2 x 512 spp (scene03)    stream (same paths: the literal gate) and on the product's Philox stream
+                                   (independent samples: the statistical gate, bound derived below);
+  K4  1 002 550 triangles          oracle BRUTE FORCE (every triangle, the reference's arithmetic) on 4 096 rays against
+                                   all three GPU traversals;
+  and every 512^2 camera batch: the exact number of rays on which the render path's traversals differ from the
+  reference-order traversal is asserted (0).
+The numbers each gate measured are written to gpurun_out/parity_fullsize.json when that directory exists.
+"""
+import json
+import math
+import os
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(ROOT, "tests", "golden")
+REPORT = {}
+
+
+def _record(key, **kw):
+    REPORT[key] = {k: (float(v) if isinstance(v, (np.floating, float)) else int(v) if isinstance(v, (np.integer, int)) else v) for k, v in kw.items()}
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        try:
+            path = os.path.join(out, "parity_fullsize.json")
+            old = json.load(open(path)) if os.path.exists(path) else {}
+            old.update(REPORT)
+            json.dump(old, open(path, "w"), indent=1, sort_keys=True)
+        except OSError:
+            pass
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def _z(gm, gm2, om, ostd, spp, scale=1.0):
+    """|gpu - oracle| / sqrt((var_o + var_g) / spp) per pixel-channel; channels where both variances vanish (pixels
+    that see only the emitter or nothing) must agree exactly and are reported separately."""
+    var_g = np.maximum(gm2.astype(np.float64) - gm.astype(np.float64) ** 2, 0.0)
+    var_o = ostd.astype(np.float64) ** 2
+    d = np.abs(gm.astype(np.float64) - om)
+    s = np.sqrt((var_o + var_g) / spp) * scale
+    flat = s < 1e-7
+    z = np.where(flat, 0.0, d / np.where(flat, 1.0, s))
+    return z, flat, d
+
+
+def test_k1_reference_stream_pixel_for_pixel(gpu, oracle, scenes):
+    """BASELINE configs[0]: Cornell box (QE/Res/scene01), 512x512, 16 spp = 16 frames with the frame seeds of
+    mt19937(1234), depth 5 -- the reference's own CPU-sized case, at its size, on the reference's own stream
+    (rtx.hlsl:61-82, :380-386; GraphicsRTX.cpp:170-171,192).  The GPU render IS the reference render: every pixel whose
+    16 paths took the same discrete decisions agrees to float rounding; an ulp in a direction (MCPT_FAST_SHADE,
+    libm) can flip a decision in a few paths, those pixels stay inside 4 sigma of their own sample variance."""
+    T, s = gpu, scenes["scene01"]
+    T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_REFERENCE)
+    W = H = 512
+    spp, depth = 16, 5
+    osum, osq, _, ocnt = oracle.scene(s).render(oracle.cfg(W, H, spp, depth))
+    om = osum / spp
+    ostd = np.sqrt(np.maximum(osq / spp - om * om, 0))
+    for flags, tag in ((0, "render path"), (T.FLAG_REF_TRAVERSAL | T.FLAG_SIMPLE_KERNEL, "reference-order traversal")):
+        gm, gm2 = T.render_scene(T.render_cfg(W, H, spp, depth, rng_mode=T.RNG_REFERENCE, flags=flags), moments=True)
+        c = T.counters()
+        assert c.paths == ocnt.paths == W * H * spp
+        equal = np.isclose(gm, om, rtol=2e-5, atol=1e-6).all(-1)
+        z, flat, d = _z(gm, gm2, om, ostd, spp)
+        rel = abs(gm.astype(np.float64).mean() - om.mean()) / om.mean()
+        _record("K1 " + tag, pixels=W * H, pixels_equal_to_rounding=equal.sum(), frac_equal=equal.mean(), mean_rel_err=rel,
+                max_z=z.max(), pixels_beyond_4_sigma=(z > 4).any(-1).sum(), rays=c.rays, oracle_rays=ocnt.rays)
+        assert equal.mean() > 0.97, equal.mean()
+        assert rel < 1e-3, rel                                    # north_star: < 1 %
+        assert abs(int(c.rays) - int(ocnt.rays)) <= 1e-3 * ocnt.rays
+        assert d[flat].max(initial=0.0) < 1e-5                    # zero-variance pixels agree outright
+        # a pixel of 16 samples in which ONE path diverged differs by at most ~ its own sample sigma (sqrt(16) = 4 standard errors)
+        assert (z > 4).any(-1).sum() <= 1e-4 * W * H, (z > 4).any(-1).sum()
+
+
+CASES = {"K2": "scene01_lambert", "K3a": "scene01", "K3b": "scene02", "S3": "scene03"}
+
+
+def _fixture(name):
+    path = os.path.join(GOLD, f"fullsize_{name}.npz")
+    if not os.path.exists(path):
+        pytest.skip(f"{path} not generated (tests/golden/make_fullsize.py)")
+    return np.load(path), json.load(open(os.path.join(GOLD, f"fullsize_{name}.json")))
+
+
+@pytest.mark.parametrize("stream", ["reference", "philox"])
+@pytest.mark.parametrize("name", list(CASES))
+def test_fullsize_image_gate(gpu, scenes, name, stream):
+    """Matched spp, full resolution, against the frozen reference render.
+
+    stream = reference: the GPU draws the reference's own numbers, so it traces the reference's paths; what is left
+      is float rounding plus the rare path whose discrete decision an ulp flipped.  Gate, literally north_star's:
+      mean relative error < 1 % (measured: < 0.01 %) and NO lattice pixel beyond 4 sigma.
+    stream = philox (the product stream): independent samples.  With N tested pixel-channels a perfect renderer
+      leaves N * erfc(4 / sqrt 2) = 6.3e-5 N of them beyond 4 sigma by chance (50 of K2's 786 432), and the sample
+      variance of a heavy-tailed per-sample distribution (Russian roulette divides by p) under-estimates sigma in
+      dark pixels, so the count is bounded by 4x the Gaussian expectation and the largest z by 7 (Gaussian
+      probability of one |z| > 7 among 10^6: 3e-6); the 4x4 tile means of the WHOLE image (16x the samples, closer
+      to Gaussian) must show at most 3x the expectation and none beyond 6."""
+    T, s = gpu, scenes[CASES[name]]
+    fx, meta = _fixture(name)
+    W, H, spp, depth, ez, stride = meta["width"], meta["height"], meta["spp"], meta["depth"], meta["eye_z"], meta["stride"]
+    T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_SAH)
+    cfg = T.render_cfg(W, H, spp, depth, seed=2024, eye=(0, 5, ez), at=(0, 5, ez - 1),
+                       rng_mode=T.RNG_REFERENCE if stream == "reference" else T.RNG_PHILOX)
+    gm, gm2 = T.render_scene(cfg, moments=True)
+    c = T.counters()
+    assert c.paths == meta["paths"]
+    assert np.isfinite(gm).all() and (gm >= 0).all()
+    rel = abs(gm.astype(np.float64).mean() - meta["image_mean"]) / meta["image_mean"]
+    rpp = c.rays / c.paths
+    # per pixel, on the lattice
+    z, flat, d = _z(gm[::stride, ::stride], gm2[::stride, ::stride], fx["lattice_mean"].astype(np.float64), fx["lattice_std"], spp)
+    n = int((~flat).sum())
+    beyond = int((z > 4).sum())
+    expect = n * math.erfc(4 / math.sqrt(2))
+    # 4x4 tile means of the whole image: variance of a tile mean = mean variance / 16
+    tm = gm.astype(np.float64).reshape(H // 4, 4, W // 4, 4, 3).mean((1, 3))
+    var_g = np.maximum(gm2.astype(np.float64) - gm.astype(np.float64) ** 2, 0).reshape(H // 4, 4, W // 4, 4, 3).mean((1, 3))
+    ts = np.sqrt((fx["tile_var"].astype(np.float64) + var_g) / (16 * spp))
+    tflat = ts < 1e-7
+    tz = np.where(tflat, 0.0, np.abs(tm - fx["tile_mean"]) / np.where(tflat, 1.0, ts))
+    tn, tbeyond = int((~tflat).sum()), int((tz > 4).sum())
+    # mean over pixels of the per-pixel relative error, where the reference pixel is not dark
+    bright = fx["tile_mean"] > 0.02
+    tile_rel = float((np.abs(tm - fx["tile_mean"])[bright] / fx["tile_mean"][bright]).mean())
+    _record(f"{name} {stream}", width=W, height=H, spp=spp, image_mean_rel_err=rel, mean_tile_rel_err=tile_rel, rays_per_path=rpp,
+            oracle_rays_per_path=meta["rays_per_path"], lattice_pixel_channels=n, beyond_4_sigma=beyond, gaussian_expectation=expect,
+            max_z=z.max(), tiles=tn, tiles_beyond_4_sigma=tbeyond, tile_gaussian_expectation=tn * math.erfc(4 / math.sqrt(2)), tile_max_z=tz.max(),
+            flat_max_abs_diff=d[flat].max(initial=0.0))
+    assert rel < 0.01, rel
+    assert tile_rel < 0.01, tile_rel
+    assert abs(rpp - meta["rays_per_path"]) < 2e-3 * meta["rays_per_path"]
+    assert d[flat].max(initial=0.0) < 2e-3      # float16 sigma rounds tiny variances to zero: such pixels are (near-)constant
+    if stream == "reference":
+        assert rel < 1e-3
+        assert beyond == 0, (beyond, z.max())   # "no pixel beyond 4 sigma"
+        assert tbeyond == 0
+    else:
+        assert beyond <= 4 * expect + 8, (beyond, expect)
+        assert z.max() < 7, z.max()
+        assert tbeyond <= 3 * tn * math.erfc(4 / math.sqrt(2)) + 4 and tz.max() < 6, (tbeyond, tz.max())
+
+
+def _random_rays(lo, hi, n, seed):
+    g = np.random.Generator(np.random.Philox(seed))
+    o = g.uniform(lo, hi, (n, 3))
+    d = g.normal(size=(n, 3))
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return np.concatenate([o, d], 1).astype(np.float32)
+
+
+def test_k4_brute_force_oracle_confirms_all_traversals(gpu, oracle, scenes):
+    """BASELINE configs[3] (1 002 550 triangles): the ORACLE'S arithmetic over every triangle of the scene -- no tree of
+    anyone's involved -- on 2 048 camera rays + 2 048 rays with origins all over the scene box, against the three GPU
+    traversals (reference-order over the reference-rule tree; stack and stackless walk over the SAH tree): id equal, t /
+    beta / gamma bit-equal.  Where the reference-ORDER traversal differs from brute force its clipped-box slab test
+    dropped a real hit; the render path's two traversals may not differ at all here."""
+    from montecarlopathtracer_b200 import scenes as S
+    from oracle.pyoracle import SceneArrays, TreeArrays
+    T, b = gpu, scenes["scene01_lambert"]
+    s = SceneArrays(*S.cornell_heightfield((b.verts, b.normals, b.tris, b.mats), 708))
+    n = len(s.tris)
+    assert n == 1002550
+    cam = T.primary_rays(T.render_cfg(1024, 1024, 1, 8, flags=T.FLAG_NO_JITTER), 0).reshape(1024, 1024, 6)
+    g = np.random.default_rng(3)
+    rays = np.concatenate([cam[g.integers(0, 1024, 2048), g.integers(0, 1024, 2048)], _random_rays(s.verts.min(0), s.verts.max(0), 2048, 17)])
+    box = np.concatenate([s.verts.min(0) - 1, s.verts.max(0) + 1]).astype(np.float32)[None]
+    one = TreeArrays(np.array([0xFFFFFFFF], np.uint32), np.array([0xFFFFFFFF], np.uint32), box, np.zeros(1, np.uint32),
+                     np.zeros(1, np.float32), np.zeros(1, np.uint32), np.array([n], np.uint32), np.arange(n, dtype=np.uint32), 0, 1)
+    btri, bt, bb, bg, cnt = oracle.scene(s, one).intersect(rays)
+    assert cnt.tris_tested == len(rays) * n
+    assert (btri >= 22).mean() > 0.2 and (btri >= 0).mean() > 0.6
+    hit = btri >= 0
+    diffs = {}
+    for mode, variant, tag in ((T.BUILD_SAH, T.ISECT_KD, "kd_stack"), (T.BUILD_SAH, T.ISECT_ROPES, "ropes"), (T.BUILD_REFERENCE, T.ISECT_REFERENCE, "reference_order")):
+        T.create_geometry(s.verts, s.normals, s.tris, s.mats, mode)
+        tri, t, be, ga = T.intersect_batch(rays, variant)
+        bad = (tri != btri) | (hit & ((_bits(t) != _bits(bt)) | (_bits(be) != _bits(bb)) | (_bits(ga) != _bits(bg))))
+        diffs[tag] = int(bad.sum())
+        if variant == T.ISECT_REFERENCE:
+            assert bad.sum() <= 2, bad.sum()
+            assert (np.where(tri[bad] >= 0, t[bad], np.inf) > bt[bad]).all()     # it MISSED a closer hit, never invented one
+        else:
+            assert bad.sum() == 0, (tag, bad.sum())
+    _record("K4 brute force", rays=len(rays), triangles=n, hits=int(hit.sum()), differing=diffs)
+
+
+@pytest.mark.parametrize("name,ez", [("scene01", 17.0), ("scene01_lambert", 17.0), ("scene02", 23.0), ("scene03", 4.75)])
+def test_camera_batch_differs_on_zero_rays(gpu, oracle, scenes, name, ez):
+    """north_star's intersection gate is on PRIMARY rays: on the 512x512 un-jittered camera batch of every scene all
+    three GPU traversals, on both trees, return the oracle's hit records bit for bit -- the count of differing rays
+    is asserted and recorded per scene (the 1e-4 allowance of the random-ray tests is not used here)."""
+    T, s = gpu, scenes[name]
+    rays = oracle.primary_rays(oracle.cfg(512, 512, 1, 5, jitter=0, eye=(0, 5, ez), at=(0, 5, ez - 1)))
+    tri, t, b, g, _ = oracle.scene(s).intersect(rays)
+    hit = tri >= 0
+    counts = {}
+    for mode, mt in ((T.BUILD_REFERENCE, "reference_tree"), (T.BUILD_SAH, "sah_tree")):
+        T.create_geometry(s.verts, s.normals, s.tris, s.mats, mode)
+        for variant, vt in ((T.ISECT_REFERENCE, "reference_order"), (T.ISECT_KD, "kd_stack"), (T.ISECT_ROPES, "ropes")):
+            gtri, gt, gb, gg = T.intersect_batch(rays, variant)
+            bad = (gtri != tri) | (hit & ((_bits(gt) != _bits(t)) | (_bits(gb) != _bits(b)) | (_bits(gg) != _bits(g))))
+            counts[f"{mt}/{vt}"] = int(bad.sum())
+    _record(f"camera_512 {name}", rays=len(rays), hits=int(hit.sum()), differing=counts)
+    assert all(v == 0 for v in counts.values()), counts

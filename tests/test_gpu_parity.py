@@ -244,9 +244,11 @@ def test_full_size_k2_properties(gpu, oracle, scenes, monkeypatch):
     assert np.isfinite(full).all() and (full >= 0).all() and full.max() > 0
     assert np.array_equal(T.render_scene(T.render_cfg(W, H, spp, 8, seed=11)), full)
     # (i) one slice per tile instead of pick_chunks' four
-    monkeypatch.setenv("MCPT_CHUNKS", "1")
-    one = T.render_scene(T.render_cfg(W, H, spp, 8, seed=11))
-    monkeypatch.delenv("MCPT_CHUNKS")
+    T.set_tuning("chunks", 1)
+    try:
+        one = T.render_scene(T.render_cfg(W, H, spp, 8, seed=11))
+    finally:
+        T.set_tuning("chunks", 0)
     assert np.allclose(one, full, rtol=2e-5, atol=1e-7)
     # (ii) halves
     a = T.render_scene(T.render_cfg(W, H, spp // 2, 8, seed=11, sample_offset=0))

@@ -131,6 +131,73 @@ def test_errors_are_reported_not_thrown_across_the_abi(tracer, scenes, tmp_path)
         tracer.get_tree()
 
 
+def test_hostile_scene_file_headers_are_refused_before_anything_is_sized(tracer, scenes, tmp_path):
+    """The counts of a .mcpt header come from an untrusted file: 7 * 2^32 uint32 of triangles must come
+    back as MCPT_ERR_IO, not as a bad_alloc / length_error that terminates the host application."""
+    import struct
+    p = tmp_path / "huge.mcpt"
+    p.write_bytes(b"MCPTSCN1" + struct.pack("<4I", 0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF, 0xFFFFFFFF) + b"\0" * 64)
+    with pytest.raises(tracer.McptError, match="header counts") as e:
+        tracer.load_scene_file(str(p))
+    assert e.value.code == 2
+    good = tmp_path / "good.mcpt"
+    scenes["scene01"].save(str(good))
+    raw = good.read_bytes()
+    (tmp_path / "short.mcpt").write_bytes(raw[:-100])          # truncated
+    (tmp_path / "long.mcpt").write_bytes(raw + b"\0" * 4)      # trailing bytes
+    for name in ("short.mcpt", "long.mcpt"):
+        with pytest.raises(tracer.McptError, match="header counts"):
+            tracer.load_scene_file(str(tmp_path / name))
+
+
+def test_failed_load_keeps_the_previous_geometry(tracer, scenes):
+    """install_scene commits only on success: after a refused scene the context still answers with the
+    previous scene's host tables AND tree, never a mix."""
+    s = scenes["scene02"]
+    tracer.create_geometry(s.verts, s.normals, s.tris, s.mats, tracer.BUILD_SAH)
+    before = (tracer.tree_info().num_nodes, tracer.get_scene()[2].copy())
+    bad = scenes["scene01"].tris.copy()
+    bad[0, 6] = 999
+    with pytest.raises(tracer.McptError, match="material index out of range"):
+        tracer.create_geometry(scenes["scene01"].verts, scenes["scene01"].normals, bad, scenes["scene01"].mats)
+    assert tracer.tree_info().num_nodes == before[0] and np.array_equal(tracer.get_scene()[2], before[1])
+    tracer.check_stackless_layout()
+    tracer.destroy_geometry()
+
+
+def test_tuning_knobs_are_explicit_clamped_and_not_environmental(tracer, scenes, monkeypatch):
+    """The shipped library reads no tuning variable from the caller's environment; knobs go through
+    mcpt_set_tuning and are clamped: a vote threshold above the warp size would make render_kernel_sm spin for ever."""
+    T = tracer
+    monkeypatch.setenv("MCPT_SM_SHADE", "99")
+    monkeypatch.setenv("MCPT_SAH_CI", "5.0")
+    monkeypatch.setenv("MCPT_CHUNKS", "3")
+    s = scenes["scene01"]
+    T.set_tuning("defaults", 0)
+    T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_SAH)
+    nodes = T.tree_info().num_nodes
+    assert (T.get_tuning("shade_threshold"), T.get_tuning("sah_ci"), T.get_tuning("chunks")) == (18, 1.0, 0)
+    for knob, value, want in (("shade_threshold", 99, 32), ("shade_threshold", -4, 1), ("cam_threshold", 1000, 32), ("tri_cap", 0, 1),
+                              ("chunks", 1 << 20, 64), ("sah_ci", 0.0, 0.05)):
+        T.set_tuning(knob, value)
+        assert T.get_tuning(knob) == pytest.approx(want)
+    with pytest.raises(T.McptError, match="unknown tuning knob"):
+        T.set_tuning("no_such_knob", 1)
+    with pytest.raises(T.McptError):
+        T.set_tuning("chunks", float("nan"))
+    # a knob that changes the tree takes effect at the next build and "defaults" restores the shipped tree
+    T.set_tuning("sah_ci", 5.0)
+    T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_SAH)
+    assert T.tree_info().num_nodes != nodes
+    T.set_tuning("defaults", 0)
+    T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_SAH)
+    assert T.tree_info().num_nodes == nodes
+    T.destroy_geometry()
+    src = "".join(open(os.path.join(ROOT, "montecarlopathtracer_b200", "csrc", f)).read()
+                  for f in os.listdir(os.path.join(ROOT, "montecarlopathtracer_b200", "csrc")) if f.endswith((".cpp", ".cu", ".cuh", ".h")))
+    assert "getenv" not in src
+
+
 def test_no_cpu_fallback(tracer, scenes):
     """Without a CUDA device every compute entry point must refuse: the product has no CPU path."""
     import torch

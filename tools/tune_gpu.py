@@ -6,6 +6,7 @@ code = r'''
 import sys; sys.path.insert(0, %r)
 from montecarlopathtracer_b200 import tracer as T
 T.initialize(0)
+T.tuning_from_env()   # the sweep's knobs arrive as MCPT_* variables of this child process
 name = %r
 if "heightfield:" in name:
     from montecarlopathtracer_b200 import scenes

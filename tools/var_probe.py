@@ -2,7 +2,7 @@
 bit-identical to the first variant's, ray counts equal; then kernel-only Mpaths/s per scene.
 
     MCPT_TUNE=1 python -m montecarlopathtracer_b200.build --force
-    python tools/var_probe.py 119 247 375 503 [--spp 256] [--k2spp 1024]     (a variant may carry knobs: 119:MCPT_SM_SHADE=18)
+    python tools/var_probe.py 119 247 375 503 [--spp 256] [--k2spp 1024]     (a variant may carry knobs: 119:shade_threshold=18)
 """
 import os, sys
 import numpy as np
@@ -16,18 +16,16 @@ if "--spp" in args: i = args.index("--spp"); spp = int(args[i + 1]); del args[i:
 if "--k2spp" in args: i = args.index("--k2spp"); k2spp = int(args[i + 1]); del args[i:i + 2]
 variants = [a for a in args]
 EYE = {"scene02": 23.0, "scene03": 4.75}
-BASE_ENV = dict(os.environ)
 
 
 def setenv(v):
+    """variant[:knob=value...] -> mcpt_set_tuning (the library does not read the environment)."""
     parts = v.split(":")
-    for k in list(os.environ):
-        if k.startswith("MCPT_") and k not in BASE_ENV:
-            del os.environ[k]
-    os.environ["MCPT_SM_VARIANT"] = parts[0]
+    T.set_tuning("defaults", 0)
+    T.set_tuning("variant", int(parts[0]))
     for kv in parts[1:]:
         k, x = kv.split("=")
-        os.environ[k] = x
+        T.set_tuning(k, float(x))
 
 
 def render(scene, w, h, n, depth=8):
