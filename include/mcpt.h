@@ -33,7 +33,7 @@ enum {
     MCPT_ERR_IO = 2,        /* file missing or malformed                */
     MCPT_ERR_CUDA = 3,      /* CUDA runtime error (text in last_error)  */
     MCPT_ERR_NO_DEVICE = 4, /* no usable GPU: the product has no CPU path */
-    MCPT_ERR_NCCL = 5,
+    MCPT_ERR_NCCL = 5,      /* libnccl.so.2 missing, or an NCCL call failed (multi-GPU entry points only) */
     MCPT_ERR_INTERNAL = 6   /* a self-check of the library's own tables failed */
 };
 
@@ -171,6 +171,28 @@ int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m
  * (a cudaStream_t, may be NULL).  Used for spp-split multi-GPU: each rank accumulates its share,
  * then one reduce of dev_sum combines them. */
 int mcpt_render_accumulate_device(const mcpt_render_cfg* cfg, void* dev_sum, void* dev_sumsq, void* stream);
+
+/* ---- multi-GPU: spp split + ONE NCCL reduce, behind the boundary ------------------
+ * The reference is single-GPU (CUTracer.cu:222 `cudaSetDevice(0)` is its only device call); this is the net-new
+ * scaling path.  One process per GPU: each calls mcpt_initialize(its device), loads the same scene, then
+ *     rank 0:  mcpt_comm_get_unique_id(id)  -> hand the 128 bytes to the other ranks (file, socket, MPI, ...)
+ *     all:     mcpt_comm_init(rank, nranks, id)
+ *     all:     mcpt_render_scene_distributed(cfg_of_the_WHOLE_job, rank == 0 ? hostcolor : NULL)
+ * Rank r renders the r-th contiguous share of cfg's sample range (mcpt_rank_share; Philox counters carry the absolute
+ * sample index, so the union over ranks is exactly the 1-GPU sample set), one ncclReduce(float4 sums, root 0) on the
+ * render stream combines the accumulation buffers over NVLink, and rank 0 normalises on the device and copies ONE
+ * float3 image to the host.  NCCL is bound at run time (dlopen libnccl.so.2): single-GPU callers need none. */
+#define MCPT_UNIQUE_ID_BYTES 128
+void mcpt_rank_share(int32_t spp, int32_t sample_offset, int rank, int nranks, int32_t* share_offset, int32_t* share_spp);
+int mcpt_comm_get_unique_id(void* id128);
+int mcpt_comm_init(int rank, int nranks, const void* id128);   /* after mcpt_initialize; nranks == 1 needs no id / no NCCL */
+int mcpt_comm_destroy(void);
+int mcpt_comm_info(int* rank, int* nranks, int* nccl_version);
+/* host_rgb (rank 0 only; others may pass NULL): width*height*3 floats, the `hostcolor` layout of RenderScene. */
+int mcpt_render_scene_distributed(const mcpt_render_cfg* whole_job, float* host_rgb);
+/* Device-resident form: ADDS this rank's share into dev_sum (width*height float4, caller-zeroed) on `stream`
+ * and reduces dev_sum in place onto rank 0. */
+int mcpt_render_accumulate_distributed_device(const mcpt_render_cfg* whole_job, void* dev_sum, void* stream);
 
 /* ---- intersection parity hook (rtx.hlsl:144-211 `intersect`) ------------------------------ */
 /* rays: 6 floats {origin, direction} each. tri = -1 on miss (t, beta, gamma = 0 then). */

@@ -32,7 +32,7 @@ CXX = "/usr/bin/g++"
 CUDA_INC = "/usr/local/cuda/include"
 
 CU_SOURCES = ["launch.cu", "parity.cu"]
-CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "kd_ropes.cpp", "obj_loader.cpp", "image_io.cpp", "abi_geometry.cpp", "abi_render.cpp"]
+CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "kd_ropes.cpp", "obj_loader.cpp", "image_io.cpp", "abi_geometry.cpp", "abi_render.cpp", "abi_dist.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-diag-suppress=549",
               "-Xcompiler", "-fPIC", "-ccbin", CXX]
 # parity.cu (kernels compared bit for bit with the CPU oracle) is never contracted; launch.cu (render kernels: the
@@ -79,7 +79,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             subprocess.check_call([CXX] + CXX_FLAGS + ["-c", os.path.join(CSRC, src), "-o", o])
     if force or _newer(LIB, objs):
         subprocess.check_call([NVCC, "-shared", "-ccbin", CXX, "-o", LIB] + objs +
-                              ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp", "-Wno-deprecated-gpu-targets"])
+                              ["-cudart", "static", "-Xcompiler", "-fopenmp", "-lgomp", "-ldl", "-Wno-deprecated-gpu-targets"])
     cli_src = os.path.join(CSRC, "cli.cpp")
     if not _NAME and (force or _newer(CLI, [cli_src, LIB] + hdrs)):   # headless driver, links only against the C ABI
         subprocess.check_call([CXX, "-std=c++17", "-O2", cli_src, "-o", CLI, "-L" + LIBDIR, "-lmcpt", "-Wl,-rpath,$ORIGIN"])

@@ -48,6 +48,9 @@ int check_cfg(const mcpt_render_cfg* cfg) {
     return MCPT_OK;
 }
 
+}  // namespace
+
+namespace mcpt {
 // Launches the path-sampling kernel for cfg and leaves per-pixel sums in *sum (and *sumsq).
 // When `dst` is given the samples are ADDED into it (multi-GPU / progressive accumulation),
 // otherwise the result pointer refers to library scratch.
@@ -163,7 +166,7 @@ int finish_counters(cudaStream_t stream) {
     return MCPT_OK;
 }
 
-}  // namespace
+}  // namespace mcpt
 
 extern "C" {
 

@@ -35,6 +35,18 @@ def rank_samples(rank: int, world: int, spp: int, scaling: str = "weak") -> tupl
     raise ValueError("scaling must be 'weak' or 'strong'")
 
 
+def comm_init_from_torch(T, dist, rank: int, world: int) -> None:
+    """Bootstraps libmcpt's own NCCL communicator (mcpt_comm_init) with torch.distributed as the side channel for the
+    128-byte id -- the only thing torch.distributed is used for on the multi-GPU path; the reduce itself runs inside
+    libmcpt.so (mcpt_render_scene_distributed).  A C++ caller hands the id over by file, socket or MPI instead."""
+    if world == 1:
+        T.comm_init(0, 1)
+        return
+    box = [T.comm_get_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    T.comm_init(rank, world, box[0])
+
+
 def reduce_accumulators(acc, dist=None, dst: int = 0):
     """The path's one exchange step: sum the per-rank (H, W, 4) float32 buffers {sum r, g, b, n} onto `dst`."""
     if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
@@ -49,17 +61,7 @@ def finalize(acc) -> np.ndarray:
     return (a[..., :3] / n).astype(np.float32)
 
 
-def render_distributed(T, cfg_kwargs: dict, width: int, height: int, spp: int, depth: int, rank: int, world: int,
-                       dist=None, scaling: str = "strong", device_index: int | None = None):
-    """Renders this rank's share on its GPU through libmcpt and reduces; returns the mean image on rank 0
-    (None elsewhere).  `T` is montecarlopathtracer_b200.tracer with the scene already loaded."""
-    import torch
-    off, n = rank_samples(rank, world, spp, scaling)
-    acc = torch.zeros(height, width, 4, device="cuda" if device_index is None else f"cuda:{device_index}", dtype=torch.float32)
-    if n > 0:
-        kw = dict(cfg_kwargs)
-        kw["sample_offset"] = kw.get("sample_offset", 0) + off
-        cfg = T.render_cfg(width, height, n, depth, **kw)
-        T.render_accumulate_device(cfg, acc.data_ptr(), 0, torch.cuda.current_stream().cuda_stream)
-    reduce_accumulators(acc, dist)
-    return finalize(acc) if rank == 0 else None
+def render_distributed(T, cfg_kwargs: dict, width: int, height: int, spp: int, depth: int):
+    """All ranks call this after comm_init_from_torch: the WHOLE job's cfg goes to mcpt_render_scene_distributed, which
+    renders this rank's share, reduces with NCCL inside libmcpt.so and returns the mean image on rank 0 (None elsewhere)."""
+    return T.render_scene_distributed(T.render_cfg(width, height, spp, depth, **cfg_kwargs))

@@ -26,6 +26,8 @@ SAMPLE_HEMI, SAMPLE_PHONG, SAMPLE_FRESNEL, SAMPLE_FRESNEL_TWIN = 0, 1, 2, 3
 ISECT_REFERENCE, ISECT_KD, ISECT_ROPES = 0, 1, 2
 TRACER_MCRT, TRACER_CUDA_TWIN = 0, 1
 ERR_NO_DEVICE = 4
+ERR_NCCL = 5
+UNIQUE_ID_BYTES = 128
 ERR_INTERNAL = 6
 
 _vp = C.c_void_p
@@ -97,6 +99,13 @@ def lib() -> C.CDLL:
     L.mcpt_selfcheck_div3.argtypes = [C.c_int64, C.c_uint32, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.mcpt_write_png.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int, C.c_float]
     L.mcpt_write_pfm.argtypes = [C.c_char_p, _vp, C.c_int, C.c_int]
+    L.mcpt_rank_share.argtypes = [C.c_int32, C.c_int32, C.c_int, C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.mcpt_rank_share.restype = None
+    L.mcpt_comm_get_unique_id.argtypes = [_vp]
+    L.mcpt_comm_init.argtypes = [C.c_int, C.c_int, _vp]
+    L.mcpt_comm_info.argtypes = [C.POINTER(C.c_int)] * 3
+    L.mcpt_render_scene_distributed.argtypes = [C.POINTER(RenderCfg), _vp]
+    L.mcpt_render_accumulate_distributed_device.argtypes = [C.POINTER(RenderCfg), _vp, _vp]
     L.mcpt_set_tuning.argtypes = [C.c_char_p, C.c_double]
     L.mcpt_get_tuning.argtypes = [C.c_char_p, C.POINTER(C.c_double)]
     L.mcpt_last_error.restype = C.c_char_p
@@ -237,6 +246,49 @@ def render_accumulate_device(cfg: RenderCfg, dev_sum_ptr: int, dev_sumsq_ptr: in
     """Adds cfg.spp samples into a caller-owned device float4 buffer (e.g. a torch tensor's data_ptr())."""
     _check(lib().mcpt_render_accumulate_device(C.byref(cfg), _vp(dev_sum_ptr), _vp(dev_sumsq_ptr or None),
                                                _vp(stream or None)))
+
+
+# ---- multi-GPU: spp split + one NCCL reduce behind the C ABI -------------------------------------
+def rank_share(spp: int, sample_offset: int, rank: int, nranks: int) -> tuple[int, int]:
+    """(sample_offset, spp) of rank `rank` when a job of `spp` samples starting at `sample_offset` is split over `nranks`."""
+    off, n = C.c_int32(), C.c_int32()
+    lib().mcpt_rank_share(spp, sample_offset, rank, nranks, C.byref(off), C.byref(n))
+    return off.value, n.value
+
+
+def comm_get_unique_id() -> bytes:
+    """Rank 0: the 128-byte NCCL id the other ranks need for comm_init (hand it over by any side channel)."""
+    buf = C.create_string_buffer(UNIQUE_ID_BYTES)
+    _check(lib().mcpt_comm_get_unique_id(buf))
+    return buf.raw
+
+
+def comm_init(rank: int, nranks: int, unique_id: bytes | None = None) -> None:
+    buf = C.create_string_buffer(unique_id, UNIQUE_ID_BYTES) if unique_id is not None else None
+    _check(lib().mcpt_comm_init(rank, nranks, buf))
+
+
+def comm_destroy() -> None:
+    _check(lib().mcpt_comm_destroy())
+
+
+def comm_info() -> tuple[int, int, int]:
+    r, n, v = C.c_int(), C.c_int(), C.c_int()
+    lib().mcpt_comm_info(C.byref(r), C.byref(n), C.byref(v))
+    return r.value, n.value, v.value
+
+
+def render_scene_distributed(whole_job: RenderCfg, out: np.ndarray | None = None):
+    """All ranks call this with the cfg of the WHOLE job; rank 0 gets hostcolor (H,W,3), the others None."""
+    rank = comm_info()[0]
+    if rank == 0 and out is None:
+        out = np.empty((whole_job.height, whole_job.width, 3), np.float32)
+    _check(lib().mcpt_render_scene_distributed(C.byref(whole_job), _p(out) if rank == 0 else None))
+    return out if rank == 0 else None
+
+
+def render_accumulate_distributed_device(whole_job: RenderCfg, dev_sum_ptr: int, stream: int = 0) -> None:
+    _check(lib().mcpt_render_accumulate_distributed_device(C.byref(whole_job), _vp(dev_sum_ptr), _vp(stream or None)))
 
 
 def intersect_batch(rays: np.ndarray, variant: int = ISECT_REFERENCE):
