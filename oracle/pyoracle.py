@@ -41,6 +41,15 @@ def build(force: bool = False) -> None:
                                           or os.path.getmtime(REF_SO) < os.path.getmtime(os.path.join(HERE, "ref_bridge.cpp"))
                                           or os.path.getmtime(REFCV_SO) < os.path.getmtime(os.path.join(HERE, "ref_bridge_cv.cpp"))):
         subprocess.check_call(["make", "-C", HERE, "ref"], stdout=subprocess.DEVNULL)
+    if os.path.isdir(REFERENCE_ROOT):
+        # the compiled drop-in proof (needs libmcpt.so) and the reference's own CUDA tracer for sm_100a (tests/test_dropin.py)
+        mcpt = os.path.join(HERE, "..", "montecarlopathtracer_b200", "lib", "libmcpt.so")
+        shim = [os.path.join(HERE, "..", "tests", "dropin", f) for f in ("CUTracerMcpt.cpp", "main_dropin.cpp")]
+        dropin, refcu = os.path.join(HERE, "_ref", "dropin_main"), os.path.join(HERE, "_ref", "cutracer_ref")
+        if os.path.exists(mcpt) and (force or not os.path.exists(dropin) or any(os.path.getmtime(f) > os.path.getmtime(dropin) for f in shim)):
+            subprocess.check_call(["make", "-C", HERE, "dropin"], stdout=subprocess.DEVNULL)
+        if force or not os.path.exists(refcu) or os.path.getmtime(shim[1]) > os.path.getmtime(refcu):
+            subprocess.check_call(["make", "-C", HERE, "refcu"], stdout=subprocess.DEVNULL)
 
 
 def _stale(so: str) -> bool:
