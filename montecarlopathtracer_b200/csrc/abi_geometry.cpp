@@ -1,6 +1,7 @@
 // C ABI, part 1: Initialize / CreateGeometry / DestroyGeometry and the scene queries.
 // Replaces PW::Tracer::Initialize, CreateGeometry, DestroyGeometry (CUTracer.cu:220-338) and the
 // static scene set-up of GraphicsRTX::DoOnUpdate (GraphicsRTX.cpp:165-167).
+#include <algorithm>
 #include <cstring>
 
 #include "context.h"
@@ -62,6 +63,7 @@ int install_scene(HostScene&& scene, int build_mode) {
     PackedScene packed;
     build_kd_tree(scene, build_mode, tree);
     if (!pack_scene(scene, tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
+    if (tuning().verify_layout && !check_ropes(tree, packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
     c.scene = std::move(scene);
     c.tree = std::move(tree);
     c.packed = std::move(packed);
@@ -104,6 +106,26 @@ int ensure_uploaded() {
     d.num_mats = static_cast<uint32_t>(c.scene.num_materials());
     d.num_emitters = c.packed.emitter_area > 0 ? static_cast<uint32_t>(c.packed.emitters.size() / 3) : 0u;
     d.emitter_area = c.packed.emitter_area;
+    // Persisting-L2 window: only when the render-path tables do not fit L2 anyway.  The set-aside is a
+    // device limit; the window itself is a per-launch attribute (launch.cu: launch_windowed).
+    c.l2_window_bytes = 0;
+    {
+        int l2 = 0, maxPersist = 0, maxWindow = 0;
+        cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, c.device);
+        cudaDeviceGetAttribute(&maxPersist, cudaDevAttrMaxPersistingL2CacheSize, c.device);
+        cudaDeviceGetAttribute(&maxWindow, cudaDevAttrMaxAccessPolicyWindowSize, c.device);
+        const size_t hot = c.packed.rope_nodes.size() * sizeof(uint2);
+        const size_t renderPath = hot + (c.packed.leaf_blob.size() + c.packed.tri_shade.size()) * sizeof(float4);
+        if (renderPath > static_cast<size_t>(l2) && maxPersist > 0 && maxWindow > 0) {
+            const size_t want = std::min<size_t>(hot, static_cast<size_t>(maxPersist));
+            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+                c.l2_window_bytes = std::min<size_t>(hot, static_cast<size_t>(maxWindow));
+                c.l2_hit_ratio = static_cast<float>(std::min(1.0, static_cast<double>(want) / static_cast<double>(c.l2_window_bytes)));
+            } else {
+                cudaGetLastError();
+            }
+        }
+    }
     c.uploaded = true;
     return MCPT_OK;
 }
@@ -298,6 +320,8 @@ int mcpt_set_tuning(const char* name, double value) {
     else if (k == "sah_resort") t.sah_resort = clampi(0, 1);
     else if (k == "build_timing") t.build_timing = clampi(0, 1);
     else if (k == "sm_stats") t.sm_stats = clampi(0, 1);
+    else if (k == "l2_persist") t.l2_persist = clampi(0, 1);
+    else if (k == "verify_layout") t.verify_layout = clampi(0, 1);
     else if (k == "sah_ci") t.sah_ci = clampf(0.05f, 100.0f);
     else if (k == "sah_eb") t.sah_eb = clampf(0.05f, 100.0f);
     else if (k == "defaults") t = Tuning();
@@ -323,6 +347,8 @@ int mcpt_get_tuning(const char* name, double* value) {
     else if (k == "sah_resort") *value = t.sah_resort;
     else if (k == "build_timing") *value = t.build_timing;
     else if (k == "sm_stats") *value = t.sm_stats;
+    else if (k == "l2_persist") *value = t.l2_persist;
+    else if (k == "verify_layout") *value = t.verify_layout;
     else if (k == "sah_ci") *value = t.sah_ci;
     else if (k == "sah_eb") *value = t.sah_eb;
     else return fail(MCPT_ERR_INVALID, "unknown tuning knob: " + k);

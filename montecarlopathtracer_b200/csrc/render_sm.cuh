@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                    LEAN = (VAR & 256) != 0;
     __shared__ float camq[CAMQ ? 7 * BLOCK : 1];  // CAMQ: parked primary ray {o, d, rng state} per thread
     bool camReady = false;
-    uint32_t st[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
+    uint32_t st[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};  // STATS: per-warp round statistics (tuning builds)
     uint32_t px, py;
     thread_pixel<BLOCK>(px, py);
     const bool inside = px < static_cast<uint32_t>(p.width) && py < static_cast<uint32_t>(p.height);
@@ -224,13 +224,6 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
         start_sample(); begin_ray();
     }
 
-    // Hop budget in warp-uniform form (ballot results live in uniform registers; a per-lane hop counter would cost a
-    // register this kernel does not have): `stall` counts consecutive TRAVERSE rounds in which the set of waiting lanes
-    // did not change, i.e. in which NO lane of the warp finished a ray.  MCPT_ROPE_MAX_HOPS such rounds mean every ray
-    // in flight has made that many hops without ending -- impossible with consistent tables (each hop moves monotonically
-    // along the ray's axes) -- so the rays are ended as misses and the host call reports MCPT_ERR_INTERNAL.
-    uint32_t prevWaiting = 0u, stall = 0u;
-
     while (true) {
         {
             // ================= SHADE: consume the hit, produce the next ray ====================
@@ -369,9 +362,11 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                     const float4 h0 = ldg4(p.sc.leaf_blob + off), h1 = ldg4(p.sc.leaf_blob + off + 1);
                     const LeafExit e = leaf_exit(p.sc, off, h0, h1, ox, oy, oz, ix, iy, iz, nearBits);
                     // No hop counter here (it costs a register the kernel does not have; intersect_ropes keeps one):
-                    // the walk terminates structurally -- GIVEN consistent tables (kd_ropes.cpp builds them; check_ropes,
-                    // exposed as mcpt_check_stackless_layout, verifies them for every scene and builder in the CPU suite).
-                    // A warp-level budget of TRAVERSE rounds (`roundsLeft`, below) bounds the kernel regardless.  The face taken on each axis is fixed by the ray's sign bits,
+                    // the walk terminates structurally -- GIVEN consistent tables.  That is a precondition this kernel depends on:
+                    // kd_ropes.cpp builds the tables, check_ropes (mcpt_check_stackless_layout) verifies them for every scene
+                    // and both builders in the CPU suite, and mcpt_set_tuning("verify_layout", 1) runs the same check on
+                    // every geometry install (0.9 s at 1 M triangles, off by default).  A warp-uniform stall counter as a
+                    // run-time net was measured: -5 % at K2 (profiles/r2_tuning.md), not shipped.  The face taken on each axis is fixed by the ray's sign bits,
                     // a rope's subtree lies wholly beyond that face, so the cell's bound on the exit axis moves
                     // strictly in the sign direction every hop whatever the float values (NaN included) and the
                     // number of hops is bounded by the number of split planes.
@@ -386,7 +381,9 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                             if (e.axis == 0u) qx = e.plane;
                             if (e.axis == 1u) qy = e.plane;
                             if (e.axis == 2u) qz = e.plane;
-                            leaf = rope_locate(p.sc, e.rope, qx, qy, qz, nearBits);
+                            uint32_t steps = 0;
+                            leaf = rope_locate(p.sc, e.rope, qx, qy, qz, nearBits, STATS ? &steps : nullptr);
+                            if (STATS) { myNodes = steps; st[10] += 1; }
                         }
                     }
                 }
@@ -395,22 +392,15 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
                 test_leaf(lend);
                 pop_or_finish();
             }
+            if (STATS && ROPES) {  // point location behind exit faces: steps summed over lanes, and the round's longest walk
+                const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, myNodes);
+                st[11] += myNodes; st[12] += mx > 0u ? 1u : 0u; st[13] += mx;
+            }
             if (STATS) {
-                st[3] += __reduce_add_sync(0xFFFFFFFFu, myNodes); st[4] += __reduce_max_sync(0xFFFFFFFFu, myNodes);
+                st[3] += __reduce_add_sync(0xFFFFFFFFu, ROPES ? 0u : myNodes); st[4] += __reduce_max_sync(0xFFFFFFFFu, ROPES ? 0u : myNodes);
                 st[5] += __reduce_add_sync(0xFFFFFFFFu, myTris); st[6] += __reduce_max_sync(0xFFFFFFFFu, myTris);
             }
-            const uint32_t waiting = __ballot_sync(0xFFFFFFFFu, state != ST_INNER && state != ST_LEAF);
-            if (ROPES) {
-                if (waiting != prevWaiting) {
-                    prevWaiting = waiting; stall = 0u;
-                } else if (++stall > MCPT_ROPE_MAX_HOPS) {
-                    if (state == ST_INNER || state == ST_LEAF) { htri = 0xFFFFFFFFu; state = ST_SHADE; }
-                    if ((threadIdx.x & 31u) == 0u) atomicExch(p.ray_counter + 15, 1ull);
-                    stall = 0u;
-                    break;
-                }
-            }
-            if (__popc(waiting) >= shadeThreshold) break;
+            if (__popc(__ballot_sync(0xFFFFFFFFu, state != ST_INNER && state != ST_LEAF)) >= shadeThreshold) break;
         }
     }
 
@@ -421,9 +411,12 @@ __global__ void __launch_bounds__(BLOCK, MIN_BLOCKS) render_kernel_sm(const Rend
     }
     if (STATS) {
         st[9] = __reduce_add_sync(0xFFFFFFFFu, st[9]);
-        if (ROPES) { st[3] = __reduce_add_sync(0xFFFFFFFFu, st[3]); st[4] = __reduce_add_sync(0xFFFFFFFFu, st[4]); }
+        if (ROPES) {
+            st[3] = __reduce_add_sync(0xFFFFFFFFu, st[3]); st[4] = __reduce_add_sync(0xFFFFFFFFu, st[4]);
+            st[10] = __reduce_add_sync(0xFFFFFFFFu, st[10]); st[11] = __reduce_add_sync(0xFFFFFFFFu, st[11]);
+        }
         if ((threadIdx.x & 31u) == 0u)
-            for (int k = 1; k < 10; ++k) atomicAdd(p.ray_counter + k, static_cast<unsigned long long>(st[k]));
+            for (int k = 1; k < 14; ++k) atomicAdd(p.ray_counter + k, static_cast<unsigned long long>(st[k]));
     }
     for (int off = 16; off > 0; off >>= 1) nrays += __shfl_xor_sync(0xFFFFFFFFu, nrays, off);
     if ((threadIdx.x & 31u) == 0u && nrays) atomicAdd(p.ray_counter, static_cast<unsigned long long>(nrays));

@@ -79,9 +79,13 @@ def test_dropin_main_renders_the_reference_workload(gpu, scenes, tmp_path, scene
     fx = os.path.join(GOLD, f"twin_reference_scene{scene_id}.npz")
     if not os.path.exists(fx):
         pytest.skip("tests/golden/twin_reference_scene*.npz not generated (tools/reference_twin.py on a GPU box)")
+    # Two independent 10 000-spp estimates (the reference's cuRAND stream is seeded from random_device): the image means agreed
+    # to 1e-4 when the fixture was made; a 40x40-pixel block mean carries ~0.3 % of Monte Carlo noise from each side.
     ref = np.load(fx)["tile_mean"].astype(np.float64)
     got = img.astype(np.float64).reshape(150, 4, 200, 4, 3).mean((1, 3))
-    assert abs(got.mean() - ref.mean()) / ref.mean() < 0.01                 # mean relative error < 1 %
-    bright = ref > 0.05 * ref.mean()
-    rel = np.abs(got - ref)[bright] / ref[bright]
-    assert rel.mean() < 0.01 and np.quantile(rel, 0.99) < 0.05, (rel.mean(), np.quantile(rel, 0.99))
+    assert abs(got.mean() - ref.mean()) / ref.mean() < 0.002                # measured 8e-5 / 1.1e-4; north_star's bar is 1 %
+    blk = lambda a: a.reshape(15, 10, 20, 10, 3).mean((1, 3))
+    bo, bg = blk(ref), blk(got)
+    bright = bo > 0.25 * ref.mean()
+    rel = np.abs(bg - bo)[bright] / bo[bright]
+    assert rel.mean() < 0.01 and rel.max() < 0.04, (rel.mean(), rel.max())

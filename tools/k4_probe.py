@@ -1,21 +1,28 @@
-"""K4 scene (1.0 M-triangle height field) probe: one scene build, a few short renders (GPU box)."""
+"""GPU box: K4 (1 002 550-triangle height field, 1024^2 x 256 spp, depth 8) kernel-only Mpaths/s against residency
+(min_blocks 4 / 5 / 6 / 8 resident 256-thread blocks per SM = 64 / 48 / 40 / 32 registers) and the persisting-L2 window
+over rope_nodes; one geometry build, images must not change (the knobs only move data and registers)."""
 import os, sys
+import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from montecarlopathtracer_b200 import tracer as T, scenes
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 708
-spp = int(sys.argv[2]) if len(sys.argv) > 2 else 16
+from montecarlopathtracer_b200 import tracer as T, scenes as S
 T.initialize(0)
-T.load_scene_file(os.path.join(ROOT, "scenes", "scene01_lambert.mcpt"), 1)
-T.create_geometry(*scenes.cornell_heightfield(T.get_scene(), n), 1)
+T.tuning_from_env()
+T.load_scene_file(os.path.join(ROOT, "scenes", "scene01_lambert.mcpt"), T.BUILD_SAH)
+T.create_geometry(*S.cornell_heightfield(T.get_scene(), 708), T.BUILD_SAH)
 i = T.tree_info()
-print(f"nodes {i.num_nodes} leaves {i.num_leaves} refs {i.num_leaf_refs} depth {i.max_depth} build {i.build_seconds:.2f}s device MB {i.device_bytes/1e6:.1f}", flush=True)
-cfg = T.render_cfg(1024, 1024, spp, 8)
-for k in range(3):
-    T.render_scene(cfg)
-    c = T.counters()
-    print(f"{c.paths / c.kernel_ms / 1e3:7.1f} Mp/s {c.rays / c.kernel_ms / 1e3:7.1f} Mr/s rays/path {c.rays / c.paths:.2f}", flush=True)
-import numpy as np
-t = T.get_tree()
-lc = t.leaf_count[t.split_axis == 0]
-print("leaf size: mean %.2f max %d, hist" % (lc.mean(), lc.max()), np.bincount(np.minimum(lc, 16)).tolist(), flush=True)
+print(f"nodes {i.num_nodes} leaves {i.num_leaves} refs {i.num_leaf_refs} depth {i.max_depth} build {i.build_seconds:.3f} s device MB {i.device_bytes / 1e6:.1f}", flush=True)
+spp = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+ref = None
+for mb in (4, 5, 6, 8):
+    for l2 in (1, 0):
+        T.set_tuning("min_blocks", mb); T.set_tuning("l2_persist", l2)
+        cfg = T.render_cfg(1024, 1024, spp, 8, seed=1)
+        img = T.render_scene(cfg)
+        best = 0.0
+        for rep in range(2):
+            T.render_scene(cfg); c = T.counters()
+            best = max(best, c.paths / c.kernel_ms / 1e3)
+        if ref is None:
+            ref = img
+        print(f"min_blocks {mb} l2_persist {l2}: {best:7.1f} Mpaths/s  {c.rays / c.kernel_ms / 1e3:7.1f} Mrays/s  image {'same' if np.array_equal(img, ref) else 'DIFFERENT'}", flush=True)
