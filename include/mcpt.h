@@ -148,6 +148,11 @@ int mcpt_get_tree_info(mcpt_tree_info* info);
  * handles, neighbour links: csrc/kd_ropes.cpp check_ropes); needs no device.  MCPT_OK, or MCPT_ERR_INTERNAL with the
  * first inconsistency in mcpt_last_error(). */
 int mcpt_check_stackless_layout(void);
+/* Diagnostic, host only: the leaves (block offsets in float4 units) the stackless walk visits for one ray {origin, direction},
+ * with each leaf's exit distance and axis, and the triangle ids those leaves hold (0xFFFFFFFF between leaves).  Mirrors the
+ * WALK of the device code operation for operation; it tests no triangle and is not a render path. */
+int mcpt_debug_stackless_walk(const float* ray6, int max_hops, int* hops, uint32_t* leaf_offsets, float* exit_t, uint32_t* exit_axis,
+                              uint32_t* tri_ids, int max_ids, int* num_ids);
 /* Copies the built tree out in the reference's BFS layout (ShaderResource.hpp:128-179);
  * any pointer may be NULL. aabb6: 6 floats per node. */
 int mcpt_get_tree(uint32_t* left, uint32_t* right, float* aabb6, uint32_t* split_axis,
@@ -232,7 +237,7 @@ int mcpt_write_pfm(const char* path, const float* rgb, int width, int height);
 /* ---- tuning / A-B knobs ---------------------------------------------------------------------- */
 /* The library never reads the caller's environment.  Knobs (clamped to their valid range): "shade_threshold",
  * "cam_threshold" [1,32], "tri_cap" [1,64], "chunks" [0,64; 0 = automatic], "sah_ci", "sah_eb" [0.05,100] (next
- * tree build), "leaf_bfs", "sah_resort", "build_timing", "sm_stats", "l2_persist", "verify_layout" {0,1}, "variant", "min_blocks" (MCPT_TUNE builds);
+ * tree build), "leaf_bfs", "sah_resort", "build_timing", "sm_stats", "verify_layout" {0,1}, "min_blocks" {0 = automatic, 4, 5, 6, 8}, "variant", "min_blocks" (MCPT_TUNE builds);
  * "defaults" restores the shipped configuration.  None of them changes a result beyond fp32 summation order. */
 int mcpt_set_tuning(const char* name, double value);
 int mcpt_get_tuning(const char* name, double* value);

@@ -106,25 +106,13 @@ int ensure_uploaded() {
     d.num_mats = static_cast<uint32_t>(c.scene.num_materials());
     d.num_emitters = c.packed.emitter_area > 0 ? static_cast<uint32_t>(c.packed.emitters.size() / 3) : 0u;
     d.emitter_area = c.packed.emitter_area;
-    // Persisting-L2 window: only when the render-path tables do not fit L2 anyway.  The set-aside is a
-    // device limit; the window itself is a per-launch attribute (launch.cu: launch_windowed).
-    c.l2_window_bytes = 0;
+    // Scenes whose render-path tables do not fit L2 are latency-bound: they render with 8 resident blocks per SM
+    // (launch.cu).  A persisting-L2 window over rope_nodes was measured there too: no effect (profiles/r2_tuning.md).
     {
-        int l2 = 0, maxPersist = 0, maxWindow = 0;
+        int l2 = 0;
         cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, c.device);
-        cudaDeviceGetAttribute(&maxPersist, cudaDevAttrMaxPersistingL2CacheSize, c.device);
-        cudaDeviceGetAttribute(&maxWindow, cudaDevAttrMaxAccessPolicyWindowSize, c.device);
-        const size_t hot = c.packed.rope_nodes.size() * sizeof(uint2);
-        const size_t renderPath = hot + (c.packed.leaf_blob.size() + c.packed.tri_shade.size()) * sizeof(float4);
-        if (renderPath > static_cast<size_t>(l2) && maxPersist > 0 && maxWindow > 0) {
-            const size_t want = std::min<size_t>(hot, static_cast<size_t>(maxPersist));
-            if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
-                c.l2_window_bytes = std::min<size_t>(hot, static_cast<size_t>(maxWindow));
-                c.l2_hit_ratio = static_cast<float>(std::min(1.0, static_cast<double>(want) / static_cast<double>(c.l2_window_bytes)));
-            } else {
-                cudaGetLastError();
-            }
-        }
+        const size_t renderPath = c.packed.rope_nodes.size() * sizeof(uint2) + (c.packed.leaf_blob.size() + c.packed.tri_shade.size()) * sizeof(float4);
+        c.large_scene = l2 > 0 && renderPath > static_cast<size_t>(l2);
     }
     c.uploaded = true;
     return MCPT_OK;
@@ -245,6 +233,33 @@ int mcpt_check_stackless_layout(void) {
     });
 }
 
+int mcpt_debug_stackless_walk(const float* ray6, int max_hops, int* hops, uint32_t* leaf_offsets, float* exit_t, uint32_t* exit_axis,
+                              uint32_t* tri_ids, int max_ids, int* num_ids) {
+    return guarded([&]() -> int {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
+    if (!ray6 || !hops || !leaf_offsets || !exit_t || !exit_axis || max_hops <= 0) return fail(MCPT_ERR_INVALID, "bad arguments");
+    *hops = walk_ropes_host(c.packed, ray6, max_hops, leaf_offsets, exit_t, exit_axis);
+    int n = 0;
+    if (tri_ids && num_ids) {   // triangle ids of the visited leaves, -1 between leaves
+        for (int h = 0; h < *hops; ++h) {
+            const uint32_t off = leaf_offsets[h];
+            uint32_t count;
+            std::memcpy(&count, &c.packed.leaf_blob[off + 1].w, 4);
+            for (uint32_t k = 0; k < count && n < max_ids; ++k) {
+                uint32_t id;
+                std::memcpy(&id, &c.packed.leaf_blob[off + 4 + 3 * k + 1].w, 4);
+                tri_ids[n++] = id;
+            }
+            if (n < max_ids) tri_ids[n++] = 0xFFFFFFFFu;
+        }
+        *num_ids = n;
+    }
+    return MCPT_OK;
+    });
+}
+
 int mcpt_get_tree_info(mcpt_tree_info* info) {
     return guarded([&]() -> int {
     Context& c = ctx();
@@ -314,13 +329,12 @@ int mcpt_set_tuning(const char* name, double value) {
     else if (k == "cam_threshold") t.cam_threshold = clampi(1, 32);
     else if (k == "tri_cap") t.tri_cap = clampi(1, 64);
     else if (k == "chunks") t.chunks = clampi(0, 64);
-    else if (k == "min_blocks") t.min_blocks = clampi(1, 16);
+    else if (k == "min_blocks") t.min_blocks = clampi(0, 16);
     else if (k == "variant") t.variant = clampi(0, 4095);
     else if (k == "leaf_bfs") t.leaf_bfs = clampi(0, 1);
     else if (k == "sah_resort") t.sah_resort = clampi(0, 1);
     else if (k == "build_timing") t.build_timing = clampi(0, 1);
     else if (k == "sm_stats") t.sm_stats = clampi(0, 1);
-    else if (k == "l2_persist") t.l2_persist = clampi(0, 1);
     else if (k == "verify_layout") t.verify_layout = clampi(0, 1);
     else if (k == "sah_ci") t.sah_ci = clampf(0.05f, 100.0f);
     else if (k == "sah_eb") t.sah_eb = clampf(0.05f, 100.0f);
@@ -347,7 +361,6 @@ int mcpt_get_tuning(const char* name, double* value) {
     else if (k == "sah_resort") *value = t.sah_resort;
     else if (k == "build_timing") *value = t.build_timing;
     else if (k == "sm_stats") *value = t.sm_stats;
-    else if (k == "l2_persist") *value = t.l2_persist;
     else if (k == "verify_layout") *value = t.verify_layout;
     else if (k == "sah_ci") *value = t.sah_ci;
     else if (k == "sah_eb") *value = t.sah_eb;

@@ -99,10 +99,7 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.shade_threshold = std::min(32, std::max(1, tn.shade_threshold));
     r.cam_threshold = std::min(32, std::max(1, tn.cam_threshold));
     r.tri_cap = std::min(64, std::max(1, tn.tri_cap));
-    if (tn.l2_persist && c.l2_window_bytes > 0) {
-        r.l2_window_ptr = c.d_rope_nodes.ptr; r.l2_window_bytes = c.l2_window_bytes; r.l2_hit_ratio = c.l2_hit_ratio;
-    }
-    r.min_blocks = tn.min_blocks;   // residency A/B (5, 6, 8) and MCPT_TUNE builds
+    r.min_blocks = tn.min_blocks > 0 ? tn.min_blocks : (c.large_scene ? 8 : 4);   // launch.cu: residency
     r.variant = tn.variant;         // MCPT_TUNE builds only
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
         // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))

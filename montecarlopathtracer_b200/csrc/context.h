@@ -44,8 +44,7 @@ struct Context {
     HostTree tree;
     PackedScene packed;
     DScene dscene{};
-    size_t l2_window_bytes = 0;   // persisting-L2 window over rope_nodes for scenes that outgrow L2 (0 = none)
-    float l2_hit_ratio = 1.0f;
+    bool large_scene = false;     // render-path tables larger than L2: latency-bound, rendered with 8 resident blocks per SM
     DeviceBuffer<float4> d_ref_nodes, d_tri_isect, d_leaf_tris, d_leaf_blob, d_tri_shade, d_mats, d_emitters;
     DeviceBuffer<uint2> d_kd_nodes, d_rope_nodes;
     DeviceBuffer<uint32_t> d_leaf_ids;

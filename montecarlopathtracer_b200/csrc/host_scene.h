@@ -44,14 +44,13 @@ struct Tuning {
     int cam_threshold = 16;    // lanes that must need a camera ray before the warp refills its queue  [1, 32]
     int tri_cap = 4;           // triangle tests per lane and round                                    [1, 64]
     int chunks = 0;            // sample slices per tile, 0 = pick_chunks' choice                      [0, 64]
-    int min_blocks = 4;        // MCPT_TUNE builds only: resident blocks per SM
+    int min_blocks = 0;        // resident 256-thread blocks per SM: 0 = automatic (4; 8 for scenes that outgrow L2), 4 / 5 / 6 / 8 force it
     int variant = 503;         // MCPT_TUNE builds only: VAR bits of render_kernel_sm
     int leaf_bfs = 0;          // A/B: breadth-first instead of depth-first device order of the leaves
     int sah_resort = 0;        // A/B: the re-sorting SAH builder on every level
     int build_timing = 0;      // print builder phase timings to stderr
     int sm_stats = 0;          // MCPT_TUNE builds, VAR bit 3: print per-warp round statistics
     int verify_layout = 0;     // run check_ropes on every geometry install (the render kernel's walk relies on consistent tables)
-    int l2_persist = 1;        // scenes whose render-path tables outgrow L2: pin rope_nodes with a persisting-L2 window
     float sah_ci = 1.0f;       // SAH: cost of a triangle test relative to a node step              [0.05, 100]
     float sah_eb = 1.0f;       // SAH: multiplier when one child is empty                            [0.05, 100]
 };

@@ -22,6 +22,7 @@
 //               low bits, no node to load; else a node index.
 //   rope_nodes  uint2 per node: inner = kd_nodes entry; leaf = {leaf handle, (count << 2) | 3}
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <string>
 #include <utility>
@@ -214,6 +215,65 @@ bool check_ropes(const HostTree& t, const PackedScene& out, std::string& err) {
         }
     }
     return true;
+}
+
+
+// Host mirror of the WALK of intersect_ropes (intersect.cuh) -- no triangle tests, same float operations (IEEE
+// reciprocal, separate multiply and add, fminf/fmaxf): the leaves a ray visits, in order, with the exit distance and axis
+// of each.  A diagnostic for the tables (mcpt_debug_stackless_walk; tests use it to show WHICH cells a ray crosses), not
+// a render path: the product traces rays on the GPU only.
+int walk_ropes_host(const PackedScene& ps, const float ray[6], int maxHops, uint32_t* leafOff, float* exitT, uint32_t* exitAxis) {
+    const float ox = ray[0], oy = ray[1], oz = ray[2], dx = ray[3], dy = ray[4], dz = ray[5];
+    const float ix = 1.0f / dx, iy = 1.0f / dy, iz = 1.0f / dz;
+    const uint32_t neg = (ix < 0.0f ? 1u : 0u) | (iy < 0.0f ? 2u : 0u) | (iz < 0.0f ? 4u : 0u);
+    const float o[3] = {ox, oy, oz}, inv[3] = {ix, iy, iz};
+    float t0 = 0.0f, t1 = 10000.0f;
+    for (int a = 0; a < 3; ++a) {
+        float tn = (ps.bmin[a] - o[a]) * inv[a], tf = (ps.bmax[a] - o[a]) * inv[a];
+        if (inv[a] < 0.0f) std::swap(tn, tf);
+        t0 = fmaxf(t0, tn); t1 = fminf(t1, tf);
+    }
+    if (!(t0 * (1.0f - 4e-7f) <= t1 * (1.0f + 4e-7f))) return 0;
+    auto locate = [&](uint32_t node, float px, float py, float pz) {
+        uint2 n = ps.rope_nodes[node];
+        while ((n.y & 3u) != 3u) {
+            const uint32_t axis = n.y & 3u;
+            const float c = axis == 0u ? px : (axis == 1u ? py : pz);
+            node = (n.y >> 2) + (c >= as_float(n.x) ? 1u : 0u);
+            n = ps.rope_nodes[node];
+        }
+        return n.x;
+    };
+    float tcur = t0;
+    float px = fminf(fmaxf(ox + t0 * dx, ps.bmin[0]), ps.bmax[0]), py = fminf(fmaxf(oy + t0 * dy, ps.bmin[1]), ps.bmax[1]),
+          pz = fminf(fmaxf(oz + t0 * dz, ps.bmin[2]), ps.bmax[2]);
+    uint32_t leaf = locate(0u, px, py, pz);
+    int hops = 0;
+    for (; hops < maxHops; ++hops) {
+        const uint32_t off = leaf & kLeafOffsetMask;
+        const float4 h0 = ps.leaf_blob[off], h1 = ps.leaf_blob[off + 1];
+        const float plx = (neg & 1u) ? h0.x : h1.x, ply = (neg & 2u) ? h0.y : h1.y, plz = (neg & 4u) ? h0.z : h1.z;
+        const float tx = (plx - ox) * ix, ty = (ply - oy) * iy, tz = (plz - oz) * iz;
+        const float te = fminf(tx, fminf(ty, tz));
+        const uint32_t axis = tx == te ? 0u : (ty == te ? 1u : 2u);
+        const float plane = axis == 0u ? plx : (axis == 1u ? ply : plz);
+        const uint32_t face = 2u * axis + (((neg >> axis) & 1u) ^ 1u);
+        uint32_t rope;
+        std::memcpy(&rope, reinterpret_cast<const char*>(&ps.leaf_blob[off + 2]) + 4 * face, 4);
+        leafOff[hops] = off; exitT[hops] = te; exitAxis[hops] = axis;
+        if (rope == kNone) { ++hops; break; }
+        tcur = fmaxf(tcur, te);
+        if (rope & kRopeIsLeaf) {
+            leaf = rope & ~kRopeIsLeaf;
+        } else {
+            px = ox + tcur * dx; py = oy + tcur * dy; pz = oz + tcur * dz;
+            if (axis == 0u) px = plane;
+            if (axis == 1u) py = plane;
+            if (axis == 2u) pz = plane;
+            leaf = locate(rope, px, py, pz);
+        }
+    }
+    return hops;
 }
 
 }  // namespace mcpt

@@ -65,26 +65,6 @@ cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
-// Launch with an optional persisting-L2 access-policy window (a per-launch attribute: independent of the stream the caller
-// hands in).  Used for scenes that outgrow L2 (K4): the point-location nodes (`rope_nodes`, 17 MB at 1 M triangles) are the
-// table every hop walks with DEPENDENT loads; pinning them keeps each step an L2 hit while the 131 MB of leaf blocks stream.
-template <class... KA, class... A>
-cudaError_t launch_windowed(void (*kernel)(KA...), dim3 grid, unsigned block, cudaStream_t stream, const RenderLaunch& r, A... args) {
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = grid; cfg.blockDim = dim3(block, 1, 1); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    if (r.l2_window_bytes > 0) {
-        attr[0].id = cudaLaunchAttributeAccessPolicyWindow;
-        attr[0].val.accessPolicyWindow.base_ptr = const_cast<void*>(r.l2_window_ptr);
-        attr[0].val.accessPolicyWindow.num_bytes = r.l2_window_bytes;
-        attr[0].val.accessPolicyWindow.hitRatio = r.l2_hit_ratio;
-        attr[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        attr[0].val.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
-        cfg.attrs = attr; cfg.numAttrs = 1;
-    }
-    return cudaLaunchKernelEx(&cfg, kernel, args...);
-}
-
 template <class RNG, bool NEE, bool MOMENTS>
 cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     RenderParams p;
@@ -99,23 +79,29 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     // removed; their numbers are in profiles/r1_tuning.md.
     if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
         switch (r.variant) {
-            case 119: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 4, 119>, grid, 256, stream, r, p, r.shade_threshold);
-            case 511: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 4, 511>, grid, 256, stream, r, p, r.shade_threshold);
+            case 119: render_kernel_sm<RNG, NEE, MOMENTS, 4, 119><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError();
+            case 511: render_kernel_sm<RNG, NEE, MOMENTS, 4, 511><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError();
+            case 1015: return r.min_blocks == 3 ? (render_kernel_sm<RNG, NEE, MOMENTS, 3, 1015><<<grid, 256, 0, stream>>>(p, r.shade_threshold), cudaGetLastError())
+                            : r.min_blocks == 8 ? (render_kernel_sm<RNG, NEE, MOMENTS, 8, 1015><<<grid, 256, 0, stream>>>(p, r.shade_threshold), cudaGetLastError())
+                                                : (render_kernel_sm<RNG, NEE, MOMENTS, 4, 1015><<<grid, 256, 0, stream>>>(p, r.shade_threshold), cudaGetLastError());
+            case 1023: render_kernel_sm<RNG, NEE, MOMENTS, 4, 1023><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError();
             default: break;
         }
     }
 #endif
-    // Residency A/B for latency-bound scenes (K4: 1 M triangles, issue slots 43 % busy): more resident warps at the price
-    // of registers (mcpt_set_tuning("min_blocks", 5 | 6 | 8); headline combination only; profiles/r2_tuning.md).
-    if constexpr (std::is_same<RNG, RngPhilox>::value && !NEE && !MOMENTS) {
+    // Residency: scenes whose render-path tables outgrow L2 (K4: 1 M triangles) are bound by the latency of dependent
+    // L2 / DRAM misses (issue slots 43 % busy at 4 blocks per SM): 8 resident blocks (32 registers, the rest spilled to L1)
+    // give +25 % there and -15 % on the L1-resident scenes.  abi_render.cpp picks 8 for large scenes (min_blocks = 0 = automatic);
+    // 5 and 6 exist for the A/B (mcpt_set_tuning("min_blocks", n); Philox stream; profiles/r2_tuning.md).
+    if constexpr (std::is_same<RNG, RngPhilox>::value) {
         switch (r.min_blocks) {
-            case 5: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 5, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
-            case 6: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 6, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
-            case 8: return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, 8, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
+            case 5: if constexpr (!NEE && !MOMENTS) { render_kernel_sm<RNG, NEE, MOMENTS, 5, MCPT_SM_VARIANT><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); } break;
+            case 6: if constexpr (!NEE && !MOMENTS) { render_kernel_sm<RNG, NEE, MOMENTS, 6, MCPT_SM_VARIANT><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError(); } break;
+            case 8: render_kernel_sm<RNG, NEE, MOMENTS, 8, MCPT_SM_VARIANT><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError();
             default: break;
         }
     }
-    return launch_windowed(render_kernel_sm<RNG, NEE, MOMENTS, MCPT_SM_MIN_BLOCKS, MCPT_SM_VARIANT>, grid, 256, stream, r, p, r.shade_threshold);
+    render_kernel_sm<RNG, NEE, MOMENTS, MCPT_SM_MIN_BLOCKS, MCPT_SM_VARIANT><<<grid, 256, 0, stream>>>(p, r.shade_threshold); return cudaGetLastError();
 }
 
 template <class RNG>

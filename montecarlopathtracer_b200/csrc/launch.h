@@ -27,9 +27,6 @@ struct RenderLaunch {
     int variant;           // tuning builds only: VAR bits of render_kernel_sm
     int cam_threshold;     // camera-ray queue refill threshold (lanes)
     int tri_cap;           // triangle tests per lane and round (VAR bit 6)
-    const void* l2_window_ptr = nullptr;  // persisting-L2 access-policy window of the launch (0 bytes = none)
-    size_t l2_window_bytes = 0;
-    float l2_hit_ratio = 1.0f;
 };
 
 // Number of kernels launched is returned through *launches (adds to it).

@@ -80,6 +80,7 @@ def lib() -> C.CDLL:
     L.mcpt_load_obj.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_int]
     L.mcpt_load_scene_file.argtypes = [C.c_char_p, C.c_int]
     L.mcpt_get_tree_info.argtypes = [C.POINTER(TreeInfo)]
+    L.mcpt_debug_stackless_walk.argtypes = [_vp, C.c_int, C.POINTER(C.c_int), _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
     L.mcpt_check_stackless_layout.argtypes = []
     L.mcpt_get_tree.argtypes = [_vp] * 8
     L.mcpt_get_scene.argtypes = [_vp] * 5
@@ -162,6 +163,23 @@ def destroy_geometry() -> None:
 def check_stackless_layout() -> None:
     """Host-side structural check of the leaf blocks and neighbour links built for the current geometry (no device)."""
     _check(lib().mcpt_check_stackless_layout())
+
+
+def debug_stackless_walk(ray, max_hops: int = 4096):
+    """Host-side diagnostic: (leaf block offsets, exit distances, exit axes, list of triangle-id lists per leaf) of the
+    stackless walk of one ray {origin, direction}; no triangle is tested, nothing runs on the device."""
+    ray = np.ascontiguousarray(ray, np.float32).reshape(6)
+    off = np.empty(max_hops, np.uint32); te = np.empty(max_hops, np.float32); ax = np.empty(max_hops, np.uint32)
+    ids = np.empty(64 * max_hops, np.uint32)
+    hops, nids = C.c_int(), C.c_int()
+    _check(lib().mcpt_debug_stackless_walk(_p(ray), max_hops, C.byref(hops), _p(off), _p(te), _p(ax), _p(ids), len(ids), C.byref(nids)))
+    leaves, cur = [], []
+    for v in ids[:nids.value]:
+        if v == 0xFFFFFFFF:
+            leaves.append(cur); cur = []
+        else:
+            cur.append(int(v))
+    return off[:hops.value], te[:hops.value], ax[:hops.value], leaves
 
 
 def tree_info() -> TreeInfo:

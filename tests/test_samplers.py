@@ -51,17 +51,20 @@ def _device(T, kind, fast):
     return T.sample_batch(kind, Z["u_fresnel"], n, d, Z["Tr"], Z["Ni"], render_arithmetic=fast), Z["fresnel_twin"]
 
 
-# Bounds (absolute, per component of a unit vector, in ulps of 1.0), set from tools/sampler_probe.py on a B200 with 2x margin.
-#   IEEE form: same expressions as the reference with round-to-nearest mul/add/div/sqrt; what differs is CUDA's
-#     sincosf / powf against the host libm the reference build used (each <= 2 ulp of its own result).
-#   render form (MCPT_FAST_SHADE): MUFU.RSQ/SQRT/RCP (<= 2 ulp), sincospif, exp2(log2 x / (Ns+1)).
-#   samplePhong at Ns = 1000: sinT = sqrt(1 - cosT^2) with cosT = x^(1/1001) within 1e-3 of 1 -- an ulp of cosT is
-#     amplified ~1/sinT^2-fold in sinT whichever implementation computes it (the reference's included), so its bound
-#     is stated separately.
-# Measured on a B200 (gpurun_out/sampler_probe.log, round 2), IEEE / render form, in ulps of 1.0:
-#   hemi 1.5 / 3.5; phong Ns <= 50: 9 / 40; phong Ns = 1000: 15 / 365; fresnel 0 (bit-equal) / 1.5.
+# Bounds (absolute, per component of a unit vector, in ulps of 1.0 = EPS), set from tools/sampler_probe.py on a B200
+# (gpurun_out/sampler_probe.log, round 2) with ~2x margin.  Measured, IEEE form / render form:
+#   hemi 1.5 / 3.5 (x 1/(1 - n.y^2) for the render form); phong Ns <= 50: 9 / 45; phong Ns = 1000: 15 / 365; fresnel 0 (bit-equal) / 36.
+#   IEEE form (parity.cu, -fmad=false): the reference's expressions with round-to-nearest mul/add/div/sqrt; what differs is
+#     CUDA's sincosf / powf against the host libm the reference build used (each <= 2 ulp of its own result).
+#   render form (launch.cu, MCPT_FAST_SHADE, -fmad=true): MUFU.RSQ/SQRT/RCP (<= 2 ulp), sincospif, exp2(log2 x / (Ns+1)), FMA
+#     contraction.  Three ill-conditioned spots are stated as such instead of hidden in one loose number:
+#       * the rotation's 1 - n.y^2 (rtx.hlsl:269/294) cancels towards the poles: any change of rounding (one FMA -- the more
+#         accurate form) moves the result by eps / (1 - n.y^2): the render-form bound carries that factor;
+#       * samplePhong at Ns = 1000: sinT = sqrt(1 - cosT^2) with cosT = x^(1/1001) within 1e-3 of 1 amplifies an ulp of cosT
+#         ~1/sinT^2-fold whichever implementation computes it (the reference's included);
+#       * sampleFresnel next to total internal reflection: sqrt(test) with test -> 0.
 BOUNDS = {  # kind -> (IEEE form, render form)
-    "hemi": (4, 8), "phong": (20, 96), "phong_ns1000": (32, 768), "fresnel": (2, 4),
+    "hemi": (4, 8), "phong": (20, 96), "phong_ns1000": (32, 768), "fresnel": (2, 64),
 }
 
 
@@ -69,24 +72,29 @@ BOUNDS = {  # kind -> (IEEE form, render form)
 @pytest.mark.parametrize("fast", [False, True], ids=["ieee", "render_arithmetic"])
 def test_device_samplers_match_reference_code(gpu, fast):
     T = gpu
+    ny = Z["normals"][:, 1].astype(np.float64)
+    special = np.abs(np.abs(ny) - 1) < 1.2e-7                    # the rotation's two exact special cases (rtx.hlsl:262-267)
+    cond = np.where(special, 1.0, 1.0 / np.maximum(1 - ny * ny, 1e-9)) if fast else np.ones_like(ny)
+    sharp = Z["Ns"] == 1000
+
     got, want = _device(T, T.SAMPLE_HEMI, fast)
-    assert np.abs(got - want).max() <= BOUNDS["hemi"][fast] * EPS
-    # the two special cases of the rotation take the reference's branches exactly
-    special = np.abs(np.abs(Z["normals"][:, 1]) - 1) < 1.2e-7
-    assert np.abs(got[special] - want[special]).max() <= BOUNDS["hemi"][fast] * EPS
+    err = np.abs(got - want).max(1)
+    assert (err <= BOUNDS["hemi"][fast] * EPS * cond).all(), (err / cond).max() / EPS
+    assert err[special].max() <= BOUNDS["hemi"][fast] * EPS       # the special cases take the reference's branches
+
     got, want = _device(T, T.SAMPLE_PHONG, fast)
     err = np.abs(got - want).max(1)
-    sharp = Z["Ns"] == 1000
-    assert err[~sharp].max() <= BOUNDS["phong"][fast] * EPS
-    assert err[sharp].max() <= BOUNDS["phong_ns1000"][fast] * EPS
+    assert (err[~sharp] <= BOUNDS["phong"][fast] * EPS * cond[~sharp]).all(), (err[~sharp] / cond[~sharp]).max() / EPS
+    assert (err[sharp] <= BOUNDS["phong_ns1000"][fast] * EPS * cond[sharp]).all(), (err[sharp] / cond[sharp]).max() / EPS
+
     got, want = _device(T, T.SAMPLE_FRESNEL_TWIN, fast)
-    assert np.abs(got - want).max() <= BOUNDS["fresnel"][fast] * EPS
-    # rtx.hlsl's own form against the oracle's restatement of it
+    assert np.abs(got - want).max() <= BOUNDS["fresnel"][fast] * EPS, np.abs(got - want).max() / EPS
+    # rtx.hlsl's own form (normalize() on every branch) against the oracle's restatement of it
     from oracle.pyoracle import Oracle
     o = Oracle()
     hl = o.sample_batch(o.FRESNEL, Z["u_fresnel"], Z["normals"], Z["dirs"], Z["Tr"], Z["Ni"])
     got = T.sample_batch(T.SAMPLE_FRESNEL, Z["u_fresnel"], Z["normals"], Z["dirs"], Z["Tr"], Z["Ni"], render_arithmetic=fast)
-    assert np.abs(got - hl).max() <= BOUNDS["fresnel"][fast] * EPS
+    assert np.abs(got - hl).max() <= BOUNDS["fresnel"][fast] * EPS, np.abs(got - hl).max() / EPS
     assert np.abs(np.linalg.norm(got.astype(np.float64), axis=1) - 1).max() < 4 * EPS
 
 

@@ -25,3 +25,12 @@ for fast in (False, True):
                 m = z["Ns"] == ns
                 line += f" | Ns={ns}: max {d[m].max():.2e}"
         print(line)
+
+# raw outputs for offline calibration of the test bounds
+out = {}
+for fast in (False, True):
+    out[f"hemi_{int(fast)}"] = T.sample_batch(T.SAMPLE_HEMI, z["u_hemi"], z["normals"], render_arithmetic=fast)
+    out[f"phong_{int(fast)}"] = T.sample_batch(T.SAMPLE_PHONG, z["u_phong"], z["normals"], z["dirs"], z["Ns"].astype(np.float32), render_arithmetic=fast)
+    out[f"fresnel_{int(fast)}"] = T.sample_batch(T.SAMPLE_FRESNEL, z["u_fresnel"], z["normals"], z["dirs"], z["Tr"], z["Ni"], render_arithmetic=fast)
+    out[f"fresnel_twin_{int(fast)}"] = T.sample_batch(T.SAMPLE_FRESNEL_TWIN, z["u_fresnel"], z["normals"], z["dirs"], z["Tr"], z["Ni"], render_arithmetic=fast)
+np.savez_compressed(os.path.join(ROOT, "gpurun_out", "sampler_outputs.npz"), **out)
