@@ -40,7 +40,9 @@ enum {
 /* KD-tree construction rule. */
 enum {
     MCPT_BUILD_REFERENCE = 0, /* node-for-node the tree of KDTree.hpp:58-287 (parity anchor) */
-    MCPT_BUILD_SAH = 1        /* this library's own O(n log n) SAH builder (same hits, other tree) */
+    MCPT_BUILD_SAH = 1,       /* this library's own O(n log n) SAH builder on the host (same hits, other tree) */
+    MCPT_BUILD_GPU = 2        /* level-synchronous SAH build on the bound device (binned above 32 references per node, exact
+                                 below): the fast ingest for large scenes (1 M triangles: ~15x the host builder); needs mcpt_initialize */
 };
 
 /* Which OBJ/MTL reader semantics mcpt_load_obj follows. */

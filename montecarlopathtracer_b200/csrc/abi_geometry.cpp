@@ -57,11 +57,16 @@ void release_device_scene(Context& c) {
 int install_scene(HostScene&& scene, int build_mode) {
     Context& c = ctx();
     std::string err;
-    if (build_mode != MCPT_BUILD_REFERENCE && build_mode != MCPT_BUILD_SAH) return fail(MCPT_ERR_INVALID, "unknown build_mode");
+    if (build_mode != MCPT_BUILD_REFERENCE && build_mode != MCPT_BUILD_SAH && build_mode != MCPT_BUILD_GPU) return fail(MCPT_ERR_INVALID, "unknown build_mode");
     if (!validate_scene(scene, err)) return fail(MCPT_ERR_INVALID, err);
     HostTree tree;
     PackedScene packed;
-    build_kd_tree(scene, build_mode, tree);
+    if (build_mode == MCPT_BUILD_GPU) {
+        if (const int rc = bind_device()) return rc;   // the device builder has no host twin to fall back on: MCPT_BUILD_SAH is the host one
+        if (!build_gpu_tree(scene, tree, err)) return fail(MCPT_ERR_CUDA, err);
+    } else {
+        build_kd_tree(scene, build_mode, tree);
+    }
     if (!pack_scene(scene, tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
     if (tuning().verify_layout && !check_ropes(tree, packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
     c.scene = std::move(scene);

@@ -59,6 +59,8 @@ Tuning& tuning();
 // kd_build.cpp
 // mode 0: node-for-node the tree of KDTree.hpp:58-287; mode 1: own SAH builder.
 void build_kd_tree(const HostScene& scene, int mode, HostTree& out);
+// kd_build_gpu.cu: level-synchronous SAH build on the bound CUDA device (MCPT_BUILD_GPU), result in the same host layout
+bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err);
 
 // scene_io.cpp
 bool load_scene_file(const std::string& path, HostScene& out, std::string& err);

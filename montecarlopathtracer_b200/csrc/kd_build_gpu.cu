@@ -1,0 +1,418 @@
+// KD-tree construction on the GPU (MCPT_BUILD_GPU) -- SURVEY.md 8(f) rank 1, first option.
+//
+// The reference builds its tree on one host thread (KDTree.hpp:58-287: 25 s at 1 M triangles); this library's host
+// SAH builder (kd_build_sah.cpp) needs 0.8 s there on 16 cores -- still twice the render it feeds (K4: 0.47 s).  Here the
+// same surface-area heuristic runs level-synchronously on the device: all nodes of one depth are split by a handful of
+// kernels, and because a level's children are allocated in the order of their parents the result IS the breadth-first,
+// children-adjacent layout the rest of the pipeline expects (ShaderResource.hpp:128-179).  Same cost model and the same
+// straddle rule as the host builders (flat on the plane -> left only, min < plane -> left, max > plane -> right):
+//   * a reference is (triangle id, node); its box is the triangle's box cut to the node's cell on the fly (nested cells:
+//     cutting to the final cell equals cutting at every level), so no per-reference boxes are stored;
+//   * nodes of more than kSmall references take the best of the kBins - 1 equidistant planes per axis, counted with one
+//     min-bin / max-bin histogram pass (Shevtsov et al. 2007); smaller nodes sweep every reference bound exactly;
+//   * cost = 1 + Ci (P_L n_L + P_R n_R) against the leaf cost Ci n (Ci from tuning().sah_ci), depth cap as the host builder.
+// The tree differs from the host SAH tree (no perfect splits: straddlers are cut as boxes, not as polygons), the hits do
+// not: every traversal returns the same closest hit on any valid tree (tests/test_gpu_builder.py).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include <cub/device/device_scan.cuh>
+
+#include "host_scene.h"
+
+namespace mcpt {
+namespace {
+
+constexpr int kBins = 32;
+constexpr uint32_t kSmall = 32;
+
+struct LevelNode {      // one node of the level being split
+    float lo[3], hi[3]; // cell
+    uint32_t begin, end;// its references in the level's reference array
+};
+
+struct Decision {       // what split_kernel decided for a level node
+    int axis;           // -1 = leaf
+    float plane;
+};
+
+#define GK_CHECK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = std::string(#x) + ": " + cudaGetErrorString(e_); return false; } } while (0)
+
+__device__ __forceinline__ float surface(const float lo[3], const float hi[3]) {
+    const float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+    return 2.0f * (x * y + y * z + z * x);
+}
+
+__global__ void tri_bounds_kernel(const float* __restrict__ verts, const uint32_t* __restrict__ tris, uint32_t nT,
+                                  float4* __restrict__ triLo, float4* __restrict__ triHi, uint32_t* __restrict__ refTri,
+                                  uint32_t* __restrict__ refNode) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nT) return;
+    float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (int k = 0; k < 3; ++k) {
+        const float* v = verts + 3 * static_cast<size_t>(tris[7 * static_cast<size_t>(t) + k]);
+        for (int i = 0; i < 3; ++i) { lo[i] = fminf(lo[i], v[i]); hi[i] = fmaxf(hi[i], v[i]); }
+    }
+    triLo[t] = make_float4(lo[0], lo[1], lo[2], 0.f);
+    triHi[t] = make_float4(hi[0], hi[1], hi[2], 0.f);
+    refTri[t] = t;
+    refNode[t] = 0u;
+}
+
+// scene box = union of the triangle boxes (one block, enough for a one-off reduction over <= a few M triangles)
+__global__ void scene_box_kernel(const float4* __restrict__ triLo, const float4* __restrict__ triHi, uint32_t nT, LevelNode* root) {
+    __shared__ float slo[3][256], shi[3][256];
+    float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (uint32_t t = threadIdx.x; t < nT; t += 256) {
+        const float4 a = triLo[t], b = triHi[t];
+        lo[0] = fminf(lo[0], a.x); lo[1] = fminf(lo[1], a.y); lo[2] = fminf(lo[2], a.z);
+        hi[0] = fmaxf(hi[0], b.x); hi[1] = fmaxf(hi[1], b.y); hi[2] = fmaxf(hi[2], b.z);
+    }
+    for (int i = 0; i < 3; ++i) { slo[i][threadIdx.x] = lo[i]; shi[i][threadIdx.x] = hi[i]; }
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s)
+            for (int i = 0; i < 3; ++i) {
+                slo[i][threadIdx.x] = fminf(slo[i][threadIdx.x], slo[i][threadIdx.x + s]);
+                shi[i][threadIdx.x] = fmaxf(shi[i][threadIdx.x], shi[i][threadIdx.x + s]);
+            }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 3; ++i) { root->lo[i] = slo[i][0]; root->hi[i] = shi[i][0]; }
+        root->begin = 0; root->end = nT;
+    }
+}
+
+// Histogram pass for the big nodes of the level: bins[node][axis][0][b] counts references whose (cut) lower bound falls in
+// bin b, [1][b] those whose upper bound does.
+__global__ void bin_kernel(const LevelNode* __restrict__ nodes, const uint32_t* __restrict__ refTri, const uint32_t* __restrict__ refNode,
+                           uint32_t nRefs, const float4* __restrict__ triLo, const float4* __restrict__ triHi,
+                           const uint32_t* __restrict__ binSlot, uint32_t* __restrict__ bins) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nRefs) return;
+    const uint32_t nd = refNode[i];
+    const uint32_t slot = binSlot[nd];
+    if (slot == 0xFFFFFFFFu) return;   // small node: exact sweep in split_kernel
+    const LevelNode n = nodes[nd];
+    const float4 a = triLo[refTri[i]], b = triHi[refTri[i]];
+    const float tlo[3] = {a.x, a.y, a.z}, thi[3] = {b.x, b.y, b.z};
+    uint32_t* base = bins + static_cast<size_t>(slot) * (3 * 2 * kBins);
+#pragma unroll
+    for (int ax = 0; ax < 3; ++ax) {
+        const float w = n.hi[ax] - n.lo[ax];
+        if (!(w > 0.0f)) continue;
+        const float s = static_cast<float>(kBins) / w;
+        const float lo = fmaxf(tlo[ax], n.lo[ax]), hi = fminf(thi[ax], n.hi[ax]);
+        const int bl = min(kBins - 1, max(0, static_cast<int>((lo - n.lo[ax]) * s)));
+        const int bh = min(kBins - 1, max(0, static_cast<int>((hi - n.lo[ax]) * s)));
+        atomicAdd(base + (ax * 2 + 0) * kBins + bl, 1u);
+        atomicAdd(base + (ax * 2 + 1) * kBins + bh, 1u);
+    }
+}
+
+// One thread per level node: SAH over the binned planes (big nodes) or over every reference bound (small nodes).
+__global__ void split_kernel(const LevelNode* __restrict__ nodes, uint32_t nNodes, const uint32_t* __restrict__ refTri,
+                             const float4* __restrict__ triLo, const float4* __restrict__ triHi, const uint32_t* __restrict__ binSlot,
+                             const uint32_t* __restrict__ bins, float ci, int canSplit, Decision* __restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nNodes) return;
+    const LevelNode n = nodes[k];
+    const uint32_t cnt = n.end - n.begin;
+    Decision d;
+    d.axis = -1; d.plane = 0.0f;
+    if (cnt == 0u || !canSplit) { out[k] = d; return; }
+    const float area = surface(n.lo, n.hi);
+    float best = ci * static_cast<float>(cnt);   // leaf cost: split only if strictly cheaper
+    if (!(area > 0.0f)) { out[k] = d; return; }
+    const float invArea = 1.0f / area;
+    auto consider = [&](int ax, float s, uint32_t nl, uint32_t nr) {
+        if (s < n.lo[ax] || s > n.hi[ax]) return;
+        if ((s <= n.lo[ax] && nr == cnt) || (s >= n.hi[ax] && nl == cnt)) return;   // a child identical to its parent: no progress
+        float llo[3] = {n.lo[0], n.lo[1], n.lo[2]}, lhi[3] = {n.hi[0], n.hi[1], n.hi[2]};
+        float rlo[3] = {n.lo[0], n.lo[1], n.lo[2]}, rhi[3] = {n.hi[0], n.hi[1], n.hi[2]};
+        lhi[ax] = s; rlo[ax] = s;
+        const float c = 1.0f + ci * (surface(llo, lhi) * invArea * static_cast<float>(nl) + surface(rlo, rhi) * invArea * static_cast<float>(nr));
+        if (c < best) { best = c; d.axis = ax; d.plane = s; }
+    };
+    const uint32_t slot = binSlot[k];
+    if (slot != 0xFFFFFFFFu) {
+        const uint32_t* base = bins + static_cast<size_t>(slot) * (3 * 2 * kBins);
+        for (int ax = 0; ax < 3; ++ax) {
+            const float w = n.hi[ax] - n.lo[ax];
+            if (!(w > 0.0f)) continue;
+            uint32_t nl = 0, nr = cnt;
+            for (int b = 1; b < kBins; ++b) {     // plane between bin b-1 and bin b
+                nl += base[(ax * 2 + 0) * kBins + (b - 1)];   // lower bound left of the plane -> goes left
+                nr -= base[(ax * 2 + 1) * kBins + (b - 1)];   // upper bound left of the plane -> does not go right
+                consider(ax, n.lo[ax] + w * (static_cast<float>(b) / static_cast<float>(kBins)), nl, nr);
+            }
+        }
+    } else {
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!(n.hi[ax] > n.lo[ax])) continue;
+            for (uint32_t i = n.begin; i < n.end; ++i) {
+                const uint32_t t = refTri[i];
+                const float4 a = triLo[t], b = triHi[t];
+                const float lo = fmaxf(ax == 0 ? a.x : (ax == 1 ? a.y : a.z), n.lo[ax]);
+                const float hi = fminf(ax == 0 ? b.x : (ax == 1 ? b.y : b.z), n.hi[ax]);
+                for (int side = 0; side < 2; ++side) {
+                    const float s = side ? hi : lo;
+                    uint32_t nl = 0, nr = 0;
+                    for (uint32_t j = n.begin; j < n.end; ++j) {
+                        const uint32_t u = refTri[j];
+                        const float4 c = triLo[u], e = triHi[u];
+                        const float l2 = fmaxf(ax == 0 ? c.x : (ax == 1 ? c.y : c.z), n.lo[ax]);
+                        const float h2 = fminf(ax == 0 ? e.x : (ax == 1 ? e.y : e.z), n.hi[ax]);
+                        if (l2 == h2 && l2 == s) { ++nl; continue; }   // flat on the plane: left only
+                        nl += l2 < s ? 1u : 0u;
+                        nr += h2 > s ? 1u : 0u;
+                    }
+                    consider(ax, s, nl, nr);
+                }
+            }
+        }
+    }
+    out[k] = d;
+}
+
+// classification of reference i against its node's plane: bit 0 left, bit 1 right (the host builders' straddle rule)
+__device__ __forceinline__ uint32_t classify(const LevelNode& n, const Decision& d, float4 a, float4 b) {
+    const int ax = d.axis;
+    const float lo = fmaxf(ax == 0 ? a.x : (ax == 1 ? a.y : a.z), n.lo[ax]);
+    const float hi = fminf(ax == 0 ? b.x : (ax == 1 ? b.y : b.z), n.hi[ax]);
+    if (lo == hi && lo == d.plane) return 1u;
+    return (lo < d.plane ? 1u : 0u) | (hi > d.plane ? 2u : 0u);
+}
+
+__global__ void count_kernel(const LevelNode* __restrict__ nodes, const Decision* __restrict__ dec, const uint32_t* __restrict__ refTri,
+                             const uint32_t* __restrict__ refNode, uint32_t nRefs, const float4* __restrict__ triLo,
+                             const float4* __restrict__ triHi, uint32_t* __restrict__ nL, uint32_t* __restrict__ nR) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nRefs) return;
+    const uint32_t nd = refNode[i];
+    const Decision d = dec[nd];
+    if (d.axis < 0) return;
+    const uint32_t c = classify(nodes[nd], d, triLo[refTri[i]], triHi[refTri[i]]);
+    if (c & 1u) atomicAdd(nL + nd, 1u);
+    if (c & 2u) atomicAdd(nR + nd, 1u);
+}
+
+// per level node: sizes that the three scans turn into offsets
+__global__ void sizes_kernel(const LevelNode* __restrict__ nodes, const Decision* __restrict__ dec, uint32_t nNodes, const uint32_t* __restrict__ nL,
+                             const uint32_t* __restrict__ nR, uint32_t* __restrict__ isSplit, uint32_t* __restrict__ childRefs, uint32_t* __restrict__ leafRefs) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nNodes) return;
+    const bool split = dec[k].axis >= 0;
+    isSplit[k] = split ? 1u : 0u;
+    childRefs[k] = split ? nL[k] + nR[k] : 0u;
+    leafRefs[k] = split ? 0u : nodes[k].end - nodes[k].begin;
+}
+
+// Writes the level's nodes into the global (breadth-first) tree and creates the next level's nodes.
+__global__ void emit_kernel(const LevelNode* __restrict__ nodes, const Decision* __restrict__ dec, uint32_t nNodes, uint32_t levelBase,
+                            uint32_t nextBase, uint32_t leafIdBase, const uint32_t* __restrict__ nL, const uint32_t* __restrict__ nR,
+                            const uint32_t* __restrict__ splitRank, const uint32_t* __restrict__ childRefOff, const uint32_t* __restrict__ leafRefOff,
+                            LevelNode* __restrict__ next, uint32_t* __restrict__ gLeft, float* __restrict__ gBox, uint32_t* __restrict__ gAxis,
+                            float* __restrict__ gPlane, uint32_t* __restrict__ gLeafOff, uint32_t* __restrict__ gLeafCnt) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nNodes) return;
+    const LevelNode n = nodes[k];
+    const Decision d = dec[k];
+    const uint32_t g = levelBase + k;
+    for (int i = 0; i < 3; ++i) { gBox[6 * static_cast<size_t>(g) + i] = n.lo[i]; gBox[6 * static_cast<size_t>(g) + 3 + i] = n.hi[i]; }
+    gLeafOff[g] = leafIdBase + leafRefOff[k];   // running count of leaf ids in front of this node (inner nodes too, as the host flatten does)
+    if (d.axis < 0) {
+        gLeft[g] = 0xFFFFFFFFu; gAxis[g] = 0u; gPlane[g] = 0.0f; gLeafCnt[g] = n.end - n.begin;
+        return;
+    }
+    const uint32_t r = splitRank[k];
+    gLeft[g] = nextBase + 2u * r; gAxis[g] = static_cast<uint32_t>(d.axis) + 1u; gPlane[g] = d.plane; gLeafCnt[g] = 0u;
+    LevelNode l = n, rr = n;
+    l.hi[d.axis] = d.plane; rr.lo[d.axis] = d.plane;
+    l.begin = childRefOff[k]; l.end = l.begin + nL[k];
+    rr.begin = l.end; rr.end = rr.begin + nR[k];
+    next[2u * r] = l; next[2u * r + 1u] = rr;
+}
+
+// Moves every reference to its place: into the child ranges of the next level (both, for a straddler) or into the leaf id list.
+__global__ void scatter_kernel(const LevelNode* __restrict__ nodes, const Decision* __restrict__ dec, const uint32_t* __restrict__ refTri,
+                               const uint32_t* __restrict__ refNode, uint32_t nRefs, const float4* __restrict__ triLo, const float4* __restrict__ triHi,
+                               const uint32_t* __restrict__ splitRank, const LevelNode* __restrict__ next, uint32_t* __restrict__ cursor /* 2 per split node */,
+                               uint32_t* __restrict__ nextTri, uint32_t* __restrict__ nextNode, uint32_t leafIdBase, const uint32_t* __restrict__ leafRefOff,
+                               uint32_t* __restrict__ leafCursor, uint32_t* __restrict__ leafIds) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nRefs) return;
+    const uint32_t nd = refNode[i], t = refTri[i];
+    const Decision d = dec[nd];
+    if (d.axis < 0) {
+        leafIds[leafIdBase + leafRefOff[nd] + atomicAdd(leafCursor + nd, 1u)] = t;
+        return;
+    }
+    const uint32_t c = classify(nodes[nd], d, triLo[t], triHi[t]);
+    const uint32_t r = splitRank[nd];
+    if (c & 1u) {
+        const uint32_t p = next[2u * r].begin + atomicAdd(cursor + 2u * r, 1u);
+        nextTri[p] = t; nextNode[p] = 2u * r;
+    }
+    if (c & 2u) {
+        const uint32_t p = next[2u * r + 1u].begin + atomicAdd(cursor + 2u * r + 1u, 1u);
+        nextTri[p] = t; nextNode[p] = 2u * r + 1u;
+    }
+}
+
+__global__ void bin_slots_kernel(const LevelNode* __restrict__ nodes, uint32_t nNodes, uint32_t* __restrict__ isBig) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < nNodes) isBig[k] = (nodes[k].end - nodes[k].begin) > kSmall ? 1u : 0u;
+}
+__global__ void bin_slots_finish_kernel(const uint32_t* __restrict__ isBig, const uint32_t* __restrict__ rank, uint32_t nNodes, uint32_t* __restrict__ slot) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < nNodes) slot[k] = isBig[k] ? rank[k] : 0xFFFFFFFFu;
+}
+
+// ascending ids inside every leaf (the scatter's atomics leave them in arrival order): the order the reference's std::set gives
+__global__ void sort_leaves_kernel(const uint32_t* __restrict__ gAxis, const uint32_t* __restrict__ gLeafOff, const uint32_t* __restrict__ gLeafCnt,
+                                   uint32_t nNodes, uint32_t* __restrict__ leafIds) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nNodes || gAxis[k] != 0u) return;
+    uint32_t* a = leafIds + gLeafOff[k];
+    const uint32_t n = gLeafCnt[k];
+    for (uint32_t i = 1; i < n; ++i) {
+        const uint32_t v = a[i];
+        uint32_t j = i;
+        while (j > 0 && a[j - 1] > v) { a[j] = a[j - 1]; --j; }
+        a[j] = v;
+    }
+}
+
+template <class T>
+struct Dev {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) { n = count; return cudaMalloc(reinterpret_cast<void**>(&p), std::max<size_t>(count, 1) * sizeof(T)); }
+    ~Dev() { if (p) cudaFree(p); }
+};
+
+}  // namespace
+
+// Needs a bound CUDA device (the caller checks).  false + err: not enough room for this scene's duplication or a CUDA error.
+bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
+    const auto t0 = std::chrono::steady_clock::now();
+    const uint32_t nT = static_cast<uint32_t>(scene.num_triangles());
+    const size_t refCap = 6ull * nT + 4096, nodeCap = 8ull * nT + 4096;
+    const float ci = tuning().sah_ci;
+    const int maxDepth = std::min(31, static_cast<int>(8.0 + 1.3 * std::log2(static_cast<double>(std::max<uint32_t>(nT, 1)))));
+    cudaStream_t s = nullptr;
+
+    Dev<float> dVerts; Dev<uint32_t> dTris; Dev<float4> triLo, triHi;
+    Dev<uint32_t> refTri[2], refNode[2];
+    Dev<LevelNode> level[2];
+    Dev<Decision> dec;
+    Dev<uint32_t> nL, nR, isSplit, childRefs, leafRefs, splitRank, childRefOff, leafRefOff, cursor, leafCursor, isBig, bigRank, binSlot, bins;
+    Dev<uint32_t> gLeft, gAxis, gLeafOff, gLeafCnt, leafIds;
+    Dev<float> gBox, gPlane;
+    Dev<unsigned char> scanTmp;
+    Dev<uint32_t> totals;   // {numSplit, childRefs total, leafRefs total, numBig} of the level
+    const size_t levelCap = refCap + 2;   // a level cannot hold more non-empty nodes than references; empty children are bounded by the split count
+    GK_CHECK(dVerts.alloc(scene.vertices.size())); GK_CHECK(dTris.alloc(scene.triangles.size()));
+    GK_CHECK(triLo.alloc(nT)); GK_CHECK(triHi.alloc(nT));
+    for (int i = 0; i < 2; ++i) { GK_CHECK(refTri[i].alloc(refCap)); GK_CHECK(refNode[i].alloc(refCap)); GK_CHECK(level[i].alloc(2 * levelCap)); }
+    GK_CHECK(dec.alloc(2 * levelCap));
+    for (Dev<uint32_t>* d : {&nL, &nR, &isSplit, &childRefs, &leafRefs, &splitRank, &childRefOff, &leafRefOff, &leafCursor, &isBig, &bigRank, &binSlot})
+        GK_CHECK(d->alloc(2 * levelCap + 1));
+    GK_CHECK(cursor.alloc(4 * levelCap + 2));
+    const size_t maxBig = refCap / kSmall + 2;
+    GK_CHECK(bins.alloc(maxBig * 3 * 2 * kBins));
+    GK_CHECK(gLeft.alloc(nodeCap)); GK_CHECK(gAxis.alloc(nodeCap)); GK_CHECK(gLeafOff.alloc(nodeCap)); GK_CHECK(gLeafCnt.alloc(nodeCap));
+    GK_CHECK(gBox.alloc(6 * nodeCap)); GK_CHECK(gPlane.alloc(nodeCap)); GK_CHECK(leafIds.alloc(refCap));
+    GK_CHECK(totals.alloc(8));
+    size_t tmpBytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmpBytes, isSplit.p, splitRank.p, static_cast<int>(2 * levelCap + 1), s);
+    GK_CHECK(scanTmp.alloc(tmpBytes + 256));
+
+    GK_CHECK(cudaMemcpyAsync(dVerts.p, scene.vertices.data(), scene.vertices.size() * 4, cudaMemcpyHostToDevice, s));
+    GK_CHECK(cudaMemcpyAsync(dTris.p, scene.triangles.data(), scene.triangles.size() * 4, cudaMemcpyHostToDevice, s));
+    const unsigned B = 256;
+    auto grid = [&](size_t n) { return static_cast<unsigned>((n + B - 1) / B); };
+    tri_bounds_kernel<<<grid(nT), B, 0, s>>>(dVerts.p, dTris.p, nT, triLo.p, triHi.p, refTri[0].p, refNode[0].p);
+    scene_box_kernel<<<1, 256, 0, s>>>(triLo.p, triHi.p, nT, level[0].p);
+
+    uint32_t nNodes = 1, nRefs = nT, levelBase = 0, leafIdBase = 0, depthReached = 0;
+    int cur = 0;
+    for (int depth = 0; nNodes > 0; ++depth) {
+        depthReached = static_cast<uint32_t>(depth);
+        const int nxt = cur ^ 1;
+        if (static_cast<size_t>(levelBase) + nNodes > nodeCap) { err = "GPU KD build: node capacity exceeded"; return false; }
+        // scan sizes include one extra element so that the last entry of each exclusive sum is the level's total
+        GK_CHECK(cudaMemsetAsync(nL.p, 0, (nNodes + 1) * 4, s)); GK_CHECK(cudaMemsetAsync(nR.p, 0, (nNodes + 1) * 4, s));
+        GK_CHECK(cudaMemsetAsync(leafCursor.p, 0, (nNodes + 1) * 4, s));
+        GK_CHECK(cudaMemsetAsync(isBig.p + nNodes, 0, 4, s));
+        bin_slots_kernel<<<grid(nNodes), B, 0, s>>>(level[cur].p, nNodes, isBig.p);
+        cub::DeviceScan::ExclusiveSum(scanTmp.p, tmpBytes, isBig.p, bigRank.p, static_cast<int>(nNodes + 1), s);
+        bin_slots_finish_kernel<<<grid(nNodes), B, 0, s>>>(isBig.p, bigRank.p, nNodes, binSlot.p);
+        uint32_t numBig = 0;
+        GK_CHECK(cudaMemcpyAsync(&numBig, bigRank.p + nNodes, 4, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaStreamSynchronize(s));
+        if (numBig > maxBig) { err = "GPU KD build: histogram capacity exceeded"; return false; }
+        if (numBig) {
+            GK_CHECK(cudaMemsetAsync(bins.p, 0, static_cast<size_t>(numBig) * 3 * 2 * kBins * 4, s));
+            bin_kernel<<<grid(nRefs), B, 0, s>>>(level[cur].p, refTri[cur].p, refNode[cur].p, nRefs, triLo.p, triHi.p, binSlot.p, bins.p);
+        }
+        split_kernel<<<grid(nNodes), B, 0, s>>>(level[cur].p, nNodes, refTri[cur].p, triLo.p, triHi.p, binSlot.p, bins.p, ci, depth < maxDepth ? 1 : 0, dec.p);
+        if (nRefs) count_kernel<<<grid(nRefs), B, 0, s>>>(level[cur].p, dec.p, refTri[cur].p, refNode[cur].p, nRefs, triLo.p, triHi.p, nL.p, nR.p);
+        GK_CHECK(cudaMemsetAsync(isSplit.p + nNodes, 0, 4, s)); GK_CHECK(cudaMemsetAsync(childRefs.p + nNodes, 0, 4, s)); GK_CHECK(cudaMemsetAsync(leafRefs.p + nNodes, 0, 4, s));
+        sizes_kernel<<<grid(nNodes), B, 0, s>>>(level[cur].p, dec.p, nNodes, nL.p, nR.p, isSplit.p, childRefs.p, leafRefs.p);
+        cub::DeviceScan::ExclusiveSum(scanTmp.p, tmpBytes, isSplit.p, splitRank.p, static_cast<int>(nNodes + 1), s);
+        cub::DeviceScan::ExclusiveSum(scanTmp.p, tmpBytes, childRefs.p, childRefOff.p, static_cast<int>(nNodes + 1), s);
+        cub::DeviceScan::ExclusiveSum(scanTmp.p, tmpBytes, leafRefs.p, leafRefOff.p, static_cast<int>(nNodes + 1), s);
+        uint32_t tot[3] = {0, 0, 0};
+        GK_CHECK(cudaMemcpyAsync(&tot[0], splitRank.p + nNodes, 4, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(&tot[1], childRefOff.p + nNodes, 4, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(&tot[2], leafRefOff.p + nNodes, 4, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaStreamSynchronize(s));
+        const uint32_t numSplit = tot[0], nextRefs = tot[1], levelLeafRefs = tot[2];
+        if (nextRefs > refCap || static_cast<size_t>(leafIdBase) + levelLeafRefs > refCap || 2ull * numSplit > 2 * levelCap) {
+            err = "GPU KD build: reference capacity exceeded (duplication above 6x)";
+            return false;
+        }
+        const uint32_t nextBase = levelBase + nNodes;
+        emit_kernel<<<grid(nNodes), B, 0, s>>>(level[cur].p, dec.p, nNodes, levelBase, nextBase, leafIdBase, nL.p, nR.p, splitRank.p, childRefOff.p, leafRefOff.p,
+                                               level[nxt].p, gLeft.p, gBox.p, gAxis.p, gPlane.p, gLeafOff.p, gLeafCnt.p);
+        if (numSplit) GK_CHECK(cudaMemsetAsync(cursor.p, 0, 2ull * numSplit * 4, s));
+        if (nRefs) scatter_kernel<<<grid(nRefs), B, 0, s>>>(level[cur].p, dec.p, refTri[cur].p, refNode[cur].p, nRefs, triLo.p, triHi.p, splitRank.p, level[nxt].p,
+                                                            cursor.p, refTri[nxt].p, refNode[nxt].p, leafIdBase, leafRefOff.p, leafCursor.p, leafIds.p);
+        leafIdBase += levelLeafRefs;
+        levelBase = nextBase;
+        nNodes = 2u * numSplit;
+        nRefs = nextRefs;
+        cur = nxt;
+    }
+    const uint32_t total = levelBase;
+    sort_leaves_kernel<<<grid(total), B, 0, s>>>(gAxis.p, gLeafOff.p, gLeafCnt.p, total, leafIds.p);
+    GK_CHECK(cudaGetLastError());
+
+    out = HostTree();
+    out.left.resize(total); out.aabb.resize(6 * static_cast<size_t>(total)); out.split_axis.resize(total); out.split_value.resize(total);
+    out.leaf_offset.resize(total); out.leaf_count.resize(total); out.leaf_ids.resize(leafIdBase);
+    GK_CHECK(cudaMemcpyAsync(out.left.data(), gLeft.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+    GK_CHECK(cudaMemcpyAsync(out.aabb.data(), gBox.p, total * 24ull, cudaMemcpyDeviceToHost, s));
+    GK_CHECK(cudaMemcpyAsync(out.split_axis.data(), gAxis.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+    GK_CHECK(cudaMemcpyAsync(out.split_value.data(), gPlane.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+    GK_CHECK(cudaMemcpyAsync(out.leaf_offset.data(), gLeafOff.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+    GK_CHECK(cudaMemcpyAsync(out.leaf_count.data(), gLeafCnt.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+    if (leafIdBase) GK_CHECK(cudaMemcpyAsync(out.leaf_ids.data(), leafIds.p, leafIdBase * 4ull, cudaMemcpyDeviceToHost, s));
+    GK_CHECK(cudaStreamSynchronize(s));
+    for (uint32_t k = 0; k < total; ++k) out.num_leaves += out.split_axis[k] == 0 ? 1u : 0u;
+    out.max_depth = depthReached;
+    out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    if (tuning().build_timing) std::fprintf(stderr, "gpu kd build: %u nodes, %u leaf refs, depth %u, %.3f s (allocation, H2D, levels, D2H)\n", total, leafIdBase, depthReached, out.build_seconds);
+    return true;
+}
+
+}  // namespace mcpt

@@ -18,7 +18,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MCPT_LIB") or os.path.join(HERE, "lib", "libmcpt.so")   # MCPT_LIB: an A/B build (build.py)
 
 # enums of include/mcpt.h
-BUILD_REFERENCE, BUILD_SAH = 0, 1
+BUILD_REFERENCE, BUILD_SAH, BUILD_GPU = 0, 1, 2
 LOADER_TINYOBJ, LOADER_OBJREADER = 0, 1
 RNG_PHILOX, RNG_REFERENCE = 0, 1
 FLAG_NEE, FLAG_MOMENTS, FLAG_NO_JITTER, FLAG_REF_TRAVERSAL, FLAG_SIMPLE_KERNEL, FLAG_RENDER_ARITHMETIC = 1, 2, 4, 8, 16, 32
