@@ -2,6 +2,8 @@
 // Replaces PW::Tracer::Initialize, CreateGeometry, DestroyGeometry (CUTracer.cu:220-338) and the
 // static scene set-up of GraphicsRTX::DoOnUpdate (GraphicsRTX.cpp:165-167).
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstring>
 
 #include "context.h"
@@ -48,6 +50,7 @@ void release_device_scene(Context& c) {
     c.d_ref_nodes.release(); c.d_kd_nodes.release(); c.d_leaf_ids.release(); c.d_tri_isect.release(); c.d_leaf_tris.release(); c.d_leaf_blob.release(); c.d_rope_nodes.release();
     c.d_tri_shade.release(); c.d_mats.release(); c.d_emitters.release();
     c.uploaded = false;
+    c.parity_uploaded = false;
 }
 
 // Builds tree and device tables into locals and commits them to the context only when all of it succeeded: a
@@ -61,41 +64,65 @@ int install_scene(HostScene&& scene, int build_mode) {
     if (!validate_scene(scene, err)) return fail(MCPT_ERR_INVALID, err);
     HostTree tree;
     PackedScene packed;
+    const auto tStart = std::chrono::steady_clock::now();
     if (build_mode == MCPT_BUILD_GPU) {
         if (const int rc = bind_device()) return rc;   // the device builder has no host twin to fall back on: MCPT_BUILD_SAH is the host one
         if (!build_gpu_tree(scene, tree, err)) return fail(MCPT_ERR_CUDA, err);
     } else {
         build_kd_tree(scene, build_mode, tree);
     }
+    const auto tTree = std::chrono::steady_clock::now();
     if (!pack_scene(scene, tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
+    const auto tPack = std::chrono::steady_clock::now();
     if (tuning().verify_layout && !check_ropes(tree, packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
     c.scene = std::move(scene);
     c.tree = std::move(tree);
     c.packed = std::move(packed);
     c.has_geometry = true;
     c.uploaded = false;
+    int rc = MCPT_OK;
     if (c.has_device) {
-        const int rc = ensure_uploaded();
+        rc = ensure_uploaded();
         if (rc != MCPT_OK) { cudaSetDevice(c.device); release_device_scene(c); }
-        return rc;
     }
-    return MCPT_OK;
+    if (tuning().build_timing) {
+        auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return 1e3 * std::chrono::duration<double>(b - a).count(); };
+        std::fprintf(stderr, "install: tree %.1f ms, pack + neighbour links %.1f ms, upload %.1f ms\n", ms(tStart, tTree), ms(tTree, tPack), ms(tPack, std::chrono::steady_clock::now()));
+    }
+    return rc;
 }
 
 }  // namespace
 
-// Host tables -> HBM.  One H2D copy per table on the context stream.
-int ensure_uploaded() {
+// Host tables -> HBM, one H2D copy per table on the context stream.  Two groups: what the render path reads (neighbour-link
+// nodes, leaf blocks, shading and material tables: 195 of 396 MB at 1 M triangles) goes up with the geometry; what only the
+// parity hooks and the A/B kernels read (reference-order boxes, stack-traversal nodes, id lists, per-triangle records) goes up
+// on their first use (ensure_parity_uploaded).
+int ensure_parity_uploaded() {
     Context& c = ctx();
-    if (const int rc = bind_device()) return rc;
-    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry: call mcpt_create_geometry / mcpt_load_obj first");
-    if (c.uploaded) return MCPT_OK;
+    if (const int rc = ensure_uploaded()) return rc;
+    if (c.parity_uploaded) return MCPT_OK;
     cudaError_t e;
     if ((e = upload(c.d_ref_nodes, c.packed.ref_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload ref_nodes");
     if ((e = upload(c.d_kd_nodes, c.packed.kd_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload kd_nodes");
     if ((e = upload(c.d_leaf_ids, c.packed.leaf_ids, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_ids");
     if ((e = upload(c.d_tri_isect, c.packed.tri_isect, c.stream)) != cudaSuccess) return fail_cuda(e, "upload tri_isect");
     if ((e = upload(c.d_leaf_tris, c.packed.leaf_tris, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_tris");
+    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "parity table upload");
+    DScene& d = c.dscene;
+    d.ref_nodes = c.d_ref_nodes.ptr; d.kd_nodes = c.d_kd_nodes.ptr; d.leaf_ids = c.d_leaf_ids.ptr; d.tri_isect = c.d_tri_isect.ptr; d.leaf_tris = c.d_leaf_tris.ptr;
+    c.parity_uploaded = true;
+    return MCPT_OK;
+}
+
+int ensure_uploaded() {
+    Context& c = ctx();
+    if (const int rc = bind_device()) return rc;
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry: call mcpt_create_geometry / mcpt_load_obj first");
+    if (c.uploaded) return MCPT_OK;
+    cudaError_t e;
+    c.parity_uploaded = false;
+    c.dscene = DScene{};
     if ((e = upload(c.d_leaf_blob, c.packed.leaf_blob, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_blob");
     if ((e = upload(c.d_rope_nodes, c.packed.rope_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload rope_nodes");
     if ((e = upload(c.d_tri_shade, c.packed.tri_shade, c.stream)) != cudaSuccess) return fail_cuda(e, "upload tri_shade");
@@ -103,8 +130,7 @@ int ensure_uploaded() {
     if ((e = upload(c.d_emitters, c.packed.emitters, c.stream)) != cudaSuccess) return fail_cuda(e, "upload emitters");
     if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "scene upload");
     DScene& d = c.dscene;
-    d.ref_nodes = c.d_ref_nodes.ptr; d.kd_nodes = c.d_kd_nodes.ptr; d.leaf_ids = c.d_leaf_ids.ptr;
-    d.tri_isect = c.d_tri_isect.ptr; d.leaf_tris = c.d_leaf_tris.ptr; d.rope_nodes = c.d_rope_nodes.ptr; d.leaf_blob = c.d_leaf_blob.ptr; d.tri_shade = c.d_tri_shade.ptr; d.mats = c.d_mats.ptr; d.emitters = c.d_emitters.ptr;
+    d.rope_nodes = c.d_rope_nodes.ptr; d.leaf_blob = c.d_leaf_blob.ptr; d.tri_shade = c.d_tri_shade.ptr; d.mats = c.d_mats.ptr; d.emitters = c.d_emitters.ptr;
     for (int i = 0; i < 3; ++i) { d.bmin[i] = c.packed.bmin[i]; d.bmax[i] = c.packed.bmax[i]; }
     d.num_nodes = static_cast<uint32_t>(c.tree.num_nodes());
     d.num_tris = static_cast<uint32_t>(c.scene.num_triangles());
@@ -161,6 +187,7 @@ int mcpt_shutdown(void) {
     if (c.has_device) {
         cudaSetDevice(c.device);
         release_device_scene(c);
+        release_gpu_builder_scratch();
         c.d_slices.release(); c.d_slices_sq.release(); c.d_sum.release(); c.d_sumsq.release(); c.d_rgb.release();
         c.d_frame_seeds.release(); c.d_counter.release(); c.d_rays.release(); c.d_t.release(); c.d_beta.release();
         c.d_gamma.release(); c.d_tri.release();

@@ -59,7 +59,8 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     Context& c = ctx();
     int rc = check_cfg(cfg);
     if (rc) return rc;
-    if ((rc = ensure_uploaded())) return rc;
+    const bool needsParityTables = (cfg->flags & (MCPT_FLAG_REF_TRAVERSAL | MCPT_FLAG_SIMPLE_KERNEL)) != 0;   // the A/B kernels walk kd_nodes / ref_nodes
+    if ((rc = needsParityTables ? ensure_parity_uploaded() : ensure_uploaded())) return rc;
     const bool moments = (cfg->flags & MCPT_FLAG_MOMENTS) != 0;
     const size_t pixels = static_cast<size_t>(cfg->width) * cfg->height;
     const int chunks = pick_chunks(cfg->width, cfg->height, cfg->spp);
@@ -236,7 +237,7 @@ int mcpt_intersect_batch_device(const void* dev_rays, int64_t n, int variant, vo
     std::lock_guard<std::mutex> g(c.lock);
     if (n < 0 || (n > 0 && (!dev_rays || !dev_tri))) return fail(MCPT_ERR_INVALID, "bad ray batch");
     if (variant != MCPT_ISECT_REFERENCE && variant != MCPT_ISECT_KD && variant != MCPT_ISECT_ROPES) return fail(MCPT_ERR_INVALID, "unknown variant");
-    int rc = ensure_uploaded();
+    int rc = variant == MCPT_ISECT_ROPES ? ensure_uploaded() : ensure_parity_uploaded();
     if (rc) return rc;
     cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : c.stream;
     c.counters.launches = 0;
@@ -350,7 +351,7 @@ int mcpt_traversal_stats(const float* rays, int64_t n, int variant, uint64_t out
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (n <= 0 || !rays || !out) return fail(MCPT_ERR_INVALID, "bad ray batch");
-    int rc = ensure_uploaded();
+    int rc = variant == MCPT_ISECT_ROPES ? ensure_uploaded() : ensure_parity_uploaded();
     if (rc) return rc;
     const size_t N = static_cast<size_t>(n);
     cudaError_t e;

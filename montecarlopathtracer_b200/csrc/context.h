@@ -39,7 +39,7 @@ struct Context {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 
-    bool has_geometry = false, uploaded = false;
+    bool has_geometry = false, uploaded = false, parity_uploaded = false;   // render-path tables / parity-hook tables in HBM
     HostScene scene;
     HostTree tree;
     PackedScene packed;
@@ -65,7 +65,8 @@ struct Context {
 Context& ctx();
 int fail(int code, const std::string& msg);
 int fail_cuda(cudaError_t e, const char* what);
-int ensure_uploaded();  // needs lock held; binds the context's device to the calling thread
+int ensure_uploaded();  // needs lock held; binds the context's device to the calling thread; render-path tables
+int ensure_parity_uploaded();  // + the tables only the parity hooks and the A/B kernels read (first use)
 int bind_device();      // cudaSetDevice(context device): the current device is per host thread, so every entry point
                         // that touches the device calls this first (MCPT_ERR_NO_DEVICE when none is bound)
 

@@ -61,6 +61,7 @@ Tuning& tuning();
 void build_kd_tree(const HostScene& scene, int mode, HostTree& out);
 // kd_build_gpu.cu: level-synchronous SAH build on the bound CUDA device (MCPT_BUILD_GPU), result in the same host layout
 bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err);
+void release_gpu_builder_scratch();   // the builder's device scratch block is kept between builds; mcpt_shutdown frees it
 
 // scene_io.cpp
 bool load_scene_file(const std::string& path, HostScene& out, std::string& err);

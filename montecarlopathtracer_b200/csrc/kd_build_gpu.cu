@@ -133,13 +133,16 @@ __global__ void split_kernel(const LevelNode* __restrict__ nodes, uint32_t nNode
     if (!(area > 0.0f)) { out[k] = d; return; }
     const float invArea = 1.0f / area;
     auto consider = [&](int ax, float s, uint32_t nl, uint32_t nr) {
+        s += 0.0f;   // -0 -> +0: two references may offer the same plane under both signs, the tie-break below cannot tell them apart
         if (s < n.lo[ax] || s > n.hi[ax]) return;
         if ((s <= n.lo[ax] && nr == cnt) || (s >= n.hi[ax] && nl == cnt)) return;   // a child identical to its parent: no progress
         float llo[3] = {n.lo[0], n.lo[1], n.lo[2]}, lhi[3] = {n.hi[0], n.hi[1], n.hi[2]};
         float rlo[3] = {n.lo[0], n.lo[1], n.lo[2]}, rhi[3] = {n.hi[0], n.hi[1], n.hi[2]};
         lhi[ax] = s; rlo[ax] = s;
         const float c = 1.0f + ci * (surface(llo, lhi) * invArea * static_cast<float>(nl) + surface(rlo, rhi) * invArea * static_cast<float>(nr));
-        if (c < best) { best = c; d.axis = ax; d.plane = s; }
+        // strict improvement, or the same cost at a smaller (axis, plane): the references of a node arrive in the order the scatter's
+        // atomics left them, the choice must not depend on it
+        if (c < best || (c == best && d.axis >= 0 && (ax < d.axis || (ax == d.axis && s < d.plane)))) { best = c; d.axis = ax; d.plane = s; }
     };
     const uint32_t slot = binSlot[k];
     if (slot != 0xFFFFFFFFu) {
@@ -180,6 +183,45 @@ __global__ void split_kernel(const LevelNode* __restrict__ nodes, uint32_t nNode
         }
     }
     out[k] = d;
+}
+
+// Big nodes choose among equidistant planes; a plane through the middle of a row of triangles cuts (duplicates) all of them,
+// while the nearest reference bound next to it usually cuts none (exactly none on grid-aligned meshes such as K4's height
+// field).  snap_kernel finds, per big node, the reference bound nearest to the chosen plane (64-bit atomicMin on
+// (distance bits, bound bits)); snap_apply_kernel moves the plane there if it lies within one bin width.
+__global__ void snap_kernel(const LevelNode* __restrict__ nodes, const Decision* __restrict__ dec, const uint32_t* __restrict__ refTri,
+                            const uint32_t* __restrict__ refNode, uint32_t nRefs, const float4* __restrict__ triLo, const float4* __restrict__ triHi,
+                            const uint32_t* __restrict__ binSlot, unsigned long long* __restrict__ snapKey) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nRefs) return;
+    const uint32_t nd = refNode[i];
+    const uint32_t slot = binSlot[nd];
+    if (slot == 0xFFFFFFFFu) return;
+    const Decision d = dec[nd];
+    if (d.axis < 0) return;
+    const LevelNode n = nodes[nd];
+    const float4 a = triLo[refTri[i]], b = triHi[refTri[i]];
+    const int ax = d.axis;
+    const float lo = fmaxf(ax == 0 ? a.x : (ax == 1 ? a.y : a.z), n.lo[ax]);
+    const float hi = fminf(ax == 0 ? b.x : (ax == 1 ? b.y : b.z), n.hi[ax]);
+    for (int side = 0; side < 2; ++side) {
+        const float c = (side ? hi : lo) + 0.0f;   // -0 -> +0
+        if (!(c > n.lo[ax] && c < n.hi[ax])) continue;   // strictly inside the cell: both children shrink
+        const unsigned long long key = (static_cast<unsigned long long>(__float_as_uint(fabsf(c - d.plane))) << 32) | __float_as_uint(c);
+        atomicMin(snapKey + slot, key);
+    }
+}
+__global__ void snap_apply_kernel(const LevelNode* __restrict__ nodes, uint32_t nNodes, const uint32_t* __restrict__ binSlot,
+                                  const unsigned long long* __restrict__ snapKey, Decision* __restrict__ dec) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nNodes) return;
+    const uint32_t slot = binSlot[k];
+    if (slot == 0xFFFFFFFFu || dec[k].axis < 0) return;
+    const unsigned long long key = snapKey[slot];
+    if (key == ~0ull) return;
+    const int ax = dec[k].axis;
+    const float w = (nodes[k].hi[ax] - nodes[k].lo[ax]) * (1.0f / kBins);
+    if (__uint_as_float(static_cast<uint32_t>(key >> 32)) <= w) dec[k].plane = __uint_as_float(static_cast<uint32_t>(key));
 }
 
 // classification of reference i against its node's plane: bit 0 left, bit 1 right (the host builders' straddle rule)
@@ -291,15 +333,43 @@ __global__ void sort_leaves_kernel(const uint32_t* __restrict__ gAxis, const uin
     }
 }
 
+// Scratch comes from ONE grow-only device block kept between builds (cudaMalloc + cudaFree of the ~2 GB a 1 M-triangle build
+// touches cost 250 ms per call -- five times the levels themselves); mcpt_shutdown releases it (release_gpu_builder_scratch).
+struct Arena {
+    char* base = nullptr;
+    size_t cap = 0, used = 0;
+} g_arena;
+
 template <class T>
 struct Dev {
     T* p = nullptr;
     size_t n = 0;
-    cudaError_t alloc(size_t count) { n = count; return cudaMalloc(reinterpret_cast<void**>(&p), std::max<size_t>(count, 1) * sizeof(T)); }
-    ~Dev() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t count) {   // sub-allocation: valid only after reserve_arena() sized the block for the whole build
+        n = count;
+        const size_t bytes = (std::max<size_t>(count, 1) * sizeof(T) + 255) & ~static_cast<size_t>(255);
+        if (g_arena.used + bytes > g_arena.cap) return cudaErrorMemoryAllocation;
+        p = reinterpret_cast<T*>(g_arena.base + g_arena.used);
+        g_arena.used += bytes;
+        return cudaSuccess;
+    }
 };
 
+cudaError_t reserve_arena(size_t bytes) {
+    g_arena.used = 0;
+    if (bytes <= g_arena.cap) return cudaSuccess;
+    if (g_arena.base) cudaFree(g_arena.base);
+    g_arena.base = nullptr; g_arena.cap = 0;
+    const cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&g_arena.base), bytes);
+    if (e == cudaSuccess) g_arena.cap = bytes;
+    return e;
+}
+
 }  // namespace
+
+void release_gpu_builder_scratch() {
+    if (g_arena.base) cudaFree(g_arena.base);
+    g_arena = Arena();
+}
 
 // Needs a bound CUDA device (the caller checks).  false + err: not enough room for this scene's duplication or a CUDA error.
 bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
@@ -318,8 +388,16 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
     Dev<uint32_t> gLeft, gAxis, gLeafOff, gLeafCnt, leafIds;
     Dev<float> gBox, gPlane;
     Dev<unsigned char> scanTmp;
-    Dev<uint32_t> totals;   // {numSplit, childRefs total, leafRefs total, numBig} of the level
+    Dev<unsigned long long> snapKey;
     const size_t levelCap = refCap + 2;   // a level cannot hold more non-empty nodes than references; empty children are bounded by the split count
+    {
+        size_t tmp = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tmp, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(2 * levelCap + 1), s);
+        const size_t need = scene.vertices.size() * 4 + scene.triangles.size() * 4 + 32ull * nT + 4 * refCap * 4 + 2 * (2 * levelCap) * sizeof(LevelNode) +
+                            2 * levelCap * sizeof(Decision) + 12 * (2 * levelCap + 1) * 4 + (4 * levelCap + 2) * 4 + (refCap / kSmall + 2) * (3 * 2 * kBins * 4 + 8) +
+                            nodeCap * (4 * 4 + 24 + 4) + refCap * 4 + tmp + 256 + 64 * 256;
+        GK_CHECK(reserve_arena(need));
+    }
     GK_CHECK(dVerts.alloc(scene.vertices.size())); GK_CHECK(dTris.alloc(scene.triangles.size()));
     GK_CHECK(triLo.alloc(nT)); GK_CHECK(triHi.alloc(nT));
     for (int i = 0; i < 2; ++i) { GK_CHECK(refTri[i].alloc(refCap)); GK_CHECK(refNode[i].alloc(refCap)); GK_CHECK(level[i].alloc(2 * levelCap)); }
@@ -331,11 +409,12 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
     GK_CHECK(bins.alloc(maxBig * 3 * 2 * kBins));
     GK_CHECK(gLeft.alloc(nodeCap)); GK_CHECK(gAxis.alloc(nodeCap)); GK_CHECK(gLeafOff.alloc(nodeCap)); GK_CHECK(gLeafCnt.alloc(nodeCap));
     GK_CHECK(gBox.alloc(6 * nodeCap)); GK_CHECK(gPlane.alloc(nodeCap)); GK_CHECK(leafIds.alloc(refCap));
-    GK_CHECK(totals.alloc(8));
+    GK_CHECK(snapKey.alloc(refCap / kSmall + 2));
     size_t tmpBytes = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, tmpBytes, isSplit.p, splitRank.p, static_cast<int>(2 * levelCap + 1), s);
     GK_CHECK(scanTmp.alloc(tmpBytes + 256));
 
+    const auto tAlloc = std::chrono::steady_clock::now();
     GK_CHECK(cudaMemcpyAsync(dVerts.p, scene.vertices.data(), scene.vertices.size() * 4, cudaMemcpyHostToDevice, s));
     GK_CHECK(cudaMemcpyAsync(dTris.p, scene.triangles.data(), scene.triangles.size() * 4, cudaMemcpyHostToDevice, s));
     const unsigned B = 256;
@@ -365,6 +444,11 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
             bin_kernel<<<grid(nRefs), B, 0, s>>>(level[cur].p, refTri[cur].p, refNode[cur].p, nRefs, triLo.p, triHi.p, binSlot.p, bins.p);
         }
         split_kernel<<<grid(nNodes), B, 0, s>>>(level[cur].p, nNodes, refTri[cur].p, triLo.p, triHi.p, binSlot.p, bins.p, ci, depth < maxDepth ? 1 : 0, dec.p);
+        if (numBig && depth < maxDepth) {
+            GK_CHECK(cudaMemsetAsync(snapKey.p, 0xFF, static_cast<size_t>(numBig) * 8, s));
+            snap_kernel<<<grid(nRefs), B, 0, s>>>(level[cur].p, dec.p, refTri[cur].p, refNode[cur].p, nRefs, triLo.p, triHi.p, binSlot.p, snapKey.p);
+            snap_apply_kernel<<<grid(nNodes), B, 0, s>>>(level[cur].p, nNodes, binSlot.p, snapKey.p, dec.p);
+        }
         if (nRefs) count_kernel<<<grid(nRefs), B, 0, s>>>(level[cur].p, dec.p, refTri[cur].p, refNode[cur].p, nRefs, triLo.p, triHi.p, nL.p, nR.p);
         GK_CHECK(cudaMemsetAsync(isSplit.p + nNodes, 0, 4, s)); GK_CHECK(cudaMemsetAsync(childRefs.p + nNodes, 0, 4, s)); GK_CHECK(cudaMemsetAsync(leafRefs.p + nNodes, 0, 4, s));
         sizes_kernel<<<grid(nNodes), B, 0, s>>>(level[cur].p, dec.p, nNodes, nL.p, nR.p, isSplit.p, childRefs.p, leafRefs.p);
@@ -394,6 +478,8 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
         cur = nxt;
     }
     const uint32_t total = levelBase;
+    GK_CHECK(cudaStreamSynchronize(s));
+    const auto tLevels = std::chrono::steady_clock::now();
     sort_leaves_kernel<<<grid(total), B, 0, s>>>(gAxis.p, gLeafOff.p, gLeafCnt.p, total, leafIds.p);
     GK_CHECK(cudaGetLastError());
 
@@ -411,7 +497,11 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
     for (uint32_t k = 0; k < total; ++k) out.num_leaves += out.split_axis[k] == 0 ? 1u : 0u;
     out.max_depth = depthReached;
     out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    if (tuning().build_timing) std::fprintf(stderr, "gpu kd build: %u nodes, %u leaf refs, depth %u, %.3f s (allocation, H2D, levels, D2H)\n", total, leafIdBase, depthReached, out.build_seconds);
+    if (tuning().build_timing) {
+        auto sec = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+        std::fprintf(stderr, "gpu kd build: %u nodes, %u leaf refs, depth %u, %.3f s = scratch allocation %.3f + H2D and levels %.3f + leaf sort and D2H %.3f\n", total,
+                     leafIdBase, depthReached, out.build_seconds, sec(t0, tAlloc), sec(tAlloc, tLevels), sec(tLevels, std::chrono::steady_clock::now()));
+    }
     return true;
 }
 
