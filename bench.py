@@ -382,7 +382,8 @@ def main():
     ap.add_argument("--workload", default="K2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override the workload's spp (a reduced-spp run is NOT the headline number)")
     ap.add_argument("--flags", default="", help="comma list: nee,ref_traversal")
-    ap.add_argument("--tree", default="sah", choices=["sah", "reference"], help="KD builder for the render path (same hits either way)")
+    ap.add_argument("--tree", default="auto", choices=["auto", "sah", "gpu", "reference"],
+                    help="KD builder for the render path (same hits whichever): auto = host SAH, device SAH builder for K4's 1 M triangles")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip other_workloads / k5_strong / multi_rank_equal")
     ap.add_argument("--tune", action="append", default=[], help="knob=value through mcpt_set_tuning (recorded in config)")
@@ -416,7 +417,13 @@ def main():
         k, _, x = kv.partition("=")
         T.set_tuning(k, float(x)); tuned[k] = T.get_tuning(k)
     M.comm_init_from_torch(T, dist, rank, world)   # libmcpt's own NCCL communicator; torch only carries the 128-byte id
-    build_mode = T.BUILD_REFERENCE if args.tree == "reference" else T.BUILD_SAH
+    def mode_for(workload):
+        if args.tree == "auto":
+            return T.BUILD_GPU if workload == "K4" else T.BUILD_SAH
+        return {"sah": T.BUILD_SAH, "gpu": T.BUILD_GPU, "reference": T.BUILD_REFERENCE}[args.tree]
+    build_mode = mode_for(args.workload)
+    tree_name = {T.BUILD_SAH: "own SAH builder on the host (MCPT_BUILD_SAH)", T.BUILD_GPU: "own SAH builder on the device (MCPT_BUILD_GPU)",
+                 T.BUILD_REFERENCE: "reference-rule tree (MCPT_BUILD_REFERENCE)"}
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     sampler = ClockSampler(local) if rank == 0 else None
     B = Bench(T, torch, dist, rank, world, sampler, flush)
@@ -429,7 +436,8 @@ def main():
         if world == 1:
             others = []
             for w, inner in (("K1", 100), ("K3a", 1), ("K3b", 1), ("K4", 1)):
-                o = B.run(w, 2, 1, 1, build_mode, flags, "weak", inner=inner)
+                o = B.run(w, 2, 1, 2 if w == "K4" else 1, mode_for(w), flags, "weak", inner=inner)
+                o["tree"] = tree_name[mode_for(w)]
                 others.append({k: v for k, v in o.items() if not k.startswith("_")})
             extras["other_workloads"] = others
         else:
@@ -461,7 +469,7 @@ def main():
                        "parallelism": f"spp-split x{world}, one ncclReduce inside libmcpt.so (NCCL {T.comm_info()[2]})" if world > 1 else "1 GPU",
                        "estimator": "NEE" if flags & T.FLAG_NEE else "emission-on-hit (reference)", "rng": "philox4x32-10",
                        "l2": "flushed between timed steps (256 MiB memset); scene is L1/L2-resident by design",
-                       "tree": "own SAH builder (MCPT_BUILD_SAH)" if build_mode == T.BUILD_SAH else "reference-rule tree (MCPT_BUILD_REFERENCE)",
+                       "tree": tree_name[build_mode],
                        "tree_nodes": m["tree_nodes"], "scene_bytes_hbm": m["scene_bytes_hbm"], "renders_per_step": m["renders_per_step"],
                        "tuning": tuned or "shipped defaults"},
             "e2e": m["e2e"], "gpu_launches": m["gpu_launches"], "clocks": m["clocks"]}

@@ -3,7 +3,9 @@
 // per-ray expressions do (rtx.hlsl:167-186 with Math.hpp:169-175's determinant order).
 #include "device_scene.h"
 
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -16,6 +18,13 @@ inline uint32_t as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u;
 
 bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) {
     const size_t nN = tree.num_nodes(), nT = scene.num_triangles(), nM = scene.num_materials();
+    auto tp = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!tuning().build_timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "  pack: %-28s %7.1f ms\n", what, 1e3 * std::chrono::duration<double>(now - tp).count());
+        tp = now;
+    };
     // Device order of the leaves: depth first (left subtree first), so that the id lists, triangle records and
     // headers of spatially neighbouring leaves are neighbours in memory (the host tree keeps the reference's
     // breadth-first leaf order).  Matters once the scene outgrows L1/L2 (K4: L2 hit rate, DRAM page locality).
@@ -48,6 +57,7 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
             }
         }
     }
+    lap("leaf order (depth first)");
     out.ref_nodes.resize(2 * nN);
     out.kd_nodes.resize(nN);
 #pragma omp parallel for schedule(static) if (nN > 65536)
@@ -72,6 +82,7 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     if (out.leaf_ids.empty()) out.leaf_ids.push_back(0u);
     for (int i = 0; i < 3; ++i) { out.bmin[i] = tree.aabb[i]; out.bmax[i] = tree.aabb[3 + i]; }
 
+    lap("node tables");
     out.tri_isect.resize(3 * nT);
     out.tri_shade.resize(3 * nT);
     out.emitters.clear();
@@ -96,6 +107,7 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         out.tri_shade[3 * t + 1] = make_float4(n1[0], n1[1], n1[2], 0.0f);
         out.tri_shade[3 * t + 2] = make_float4(n2[0], n2[1], n2[2], 0.0f);
     }
+    lap("triangle tables");
     for (size_t t = 0; t < nT; ++t) {  // emitters keep triangle order: sequential
         const uint32_t* r = &scene.triangles[7 * t];
         const float* a = &scene.vertices[3 * static_cast<size_t>(r[0])];
@@ -115,12 +127,15 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
             out.emitters.push_back(make_float4(static_cast<float>(v[0]), static_cast<float>(v[1]), static_cast<float>(v[2]), as_float(static_cast<uint32_t>(t))));
         }
     }
+    lap("emitters");
     out.leaf_tris.resize(3 * out.leaf_ids.size());
 #pragma omp parallel for schedule(static) if (out.leaf_ids.size() > 65536)
     for (size_t k = 0; k < out.leaf_ids.size(); ++k)
         for (int j = 0; j < 3; ++j) out.leaf_tris[3 * k + j] = out.tri_isect[3 * static_cast<size_t>(out.leaf_ids[k]) + j];
 
+    lap("leaf records");
     const bool ropesOk = build_ropes(tree, out);
+    lap("neighbour links + leaf blocks");
 
     // running CDF over emitter area for area-uniform light sampling
     double run = 0.0;

@@ -17,7 +17,17 @@ lo, hi = verts.min(0), verts.max(0)
 o = g.uniform(lo, hi, (1 << 20, 3))
 d = g.normal(size=(1 << 20, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
 inc = np.concatenate([o, d], 1).astype(np.float32)
-for name, rays in (("camera", cam), ("incoherent", inc)):
+# (c) the same incoherent rays SORTED the way a wavefront tracer would sort its bounce queue: direction octant, then a 30-bit
+# Morton code of the origin -- rays that start in the same region and head the same way become neighbours in a warp
+def morton30(p):
+    q = np.clip(((p - lo) / (hi - lo) * 1023.0), 0, 1023).astype(np.uint64)
+    def spread(v):
+        v = (v | (v << 16)) & 0x030000FF; v = (v | (v << 8)) & 0x0300F00F; v = (v | (v << 4)) & 0x030C30C3; v = (v | (v << 2)) & 0x09249249
+        return v
+    return spread(q[:, 0]) | (spread(q[:, 1]) << 1) | (spread(q[:, 2]) << 2)
+octant = ((inc[:, 3] < 0).astype(np.uint64) | ((inc[:, 4] < 0).astype(np.uint64) << 1) | ((inc[:, 5] < 0).astype(np.uint64) << 2))
+srt = inc[np.argsort((octant << 30) | morton30(inc[:, :3].astype(np.float64)), kind="stable")]
+for name, rays in (("camera", cam), ("incoherent", inc), ("incoherent sorted by octant + Morton(origin)", srt)):
     for variant in (T.ISECT_ROPES, T.ISECT_KD):
         tri, t, b, gm = T.intersect_batch(rays, variant)
         print(name, "variant", variant, "hits", int((tri >= 0).sum()), "of", len(rays), flush=True)
