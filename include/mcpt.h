@@ -178,6 +178,19 @@ int mcpt_render_scene(const mcpt_render_cfg* cfg, float* host_rgb, float* host_m
  * (a cudaStream_t, may be NULL).  Used for spp-split multi-GPU: each rank accumulates its share,
  * then one reduce of dev_sum combines them. */
 int mcpt_render_accumulate_device(const mcpt_render_cfg* cfg, void* dev_sum, void* dev_sumsq, void* stream);
+/* No counterpart in the reference.  mcpt_render_accumulate_device(cfg,
+ * dev_sum, NULL, stream) for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses
+ * that forbid it): this call allocates NOTHING on the device (no cudaMalloc, cudaFree or allocating library routine).
+ * The slice scratch of the render kernel and its counters live in one fixed `static __device__` array of
+ * 256 B + MCPT_NOALLOC_MAX_SLICE_PIXELS * 16 B (16 MiB) that every GPU loading the library holds until exit
+ * (csrc/noalloc.cu).  Limits: width*height <= MCPT_NOALLOC_MAX_SLICE_PIXELS (MCPT_ERR_INVALID beyond it);
+ * MCPT_RNG_PHILOX only; no MCPT_FLAG_MOMENTS / REF_TRAVERSAL / SIMPLE_KERNEL; the geometry must already be resident
+ * (loaded after mcpt_initialize: this call uploads nothing).  Same samples as the allocating entry point; the same
+ * bits too whenever width*height*slices fits the scratch with the slice count that one picks, otherwise fewer slices
+ * (another fp32 summation order).  All calls share the one array, which keeps the last call's contents (the call
+ * clears what must start at zero): calls that overlap on the GPU would race, so the call is blocking and serialised. */
+#define MCPT_NOALLOC_MAX_SLICE_PIXELS (1u << 20)
+int mcpt_render_accumulate_device_noalloc(const mcpt_render_cfg* cfg, void* dev_sum, void* stream);
 
 /* ---- multi-GPU: spp split + ONE NCCL reduce, behind the boundary ------------------
  * The reference is single-GPU (CUTracer.cu:222 `cudaSetDevice(0)` is its only device call); this is the net-new

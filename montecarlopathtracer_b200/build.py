@@ -31,13 +31,13 @@ NVCC = os.environ.get("MCPT_NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = "/usr/bin/g++"
 CUDA_INC = "/usr/local/cuda/include"
 
-CU_SOURCES = ["launch.cu", "parity.cu", "kd_build_gpu.cu"]
+CU_SOURCES = ["launch.cu", "parity.cu", "kd_build_gpu.cu", "noalloc.cu"]
 CPP_SOURCES = ["kd_build.cpp", "kd_build_sah.cpp", "scene_io.cpp", "device_scene.cpp", "kd_ropes.cpp", "obj_loader.cpp", "image_io.cpp", "abi_geometry.cpp", "abi_render.cpp", "abi_dist.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-std=c++17", "-O3", "-lineinfo", "-diag-suppress=549",
               "-Xcompiler", "-fPIC", "-ccbin", CXX]
 # parity.cu (kernels compared bit for bit with the CPU oracle) is never contracted; launch.cu (render kernels: the
 # triangle test is explicit _rn intrinsics, shading uses the hardware units) takes MCPT_FMAD (profiles/r2_tuning.md).
-FMAD = {"launch.cu": os.environ.get("MCPT_FMAD", "true"), "parity.cu": "false", "kd_build_gpu.cu": "false"}
+FMAD = {"launch.cu": os.environ.get("MCPT_FMAD", "true"), "parity.cu": "false", "kd_build_gpu.cu": "false", "noalloc.cu": "false"}
 CXX_FLAGS = ["-std=c++17", "-O2", "-fPIC", "-fopenmp", "-ffp-contract=off", "-Wall", "-I" + CUDA_INC]
 
 

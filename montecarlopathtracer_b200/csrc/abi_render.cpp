@@ -12,7 +12,7 @@
 
 using namespace mcpt;
 
-namespace {
+namespace mcpt {
 
 // How many slices the spp of a pixel are cut into (grid.z; each slice accumulates into its own buffer, one
 // reduce pass adds them).  Two reasons to cut: (1) small images: enough threads to fill 148 SMs several times
@@ -48,9 +48,6 @@ int check_cfg(const mcpt_render_cfg* cfg) {
     return MCPT_OK;
 }
 
-}  // namespace
-
-namespace mcpt {
 // Launches the path-sampling kernel for cfg and leaves per-pixel sums in *sum (and *sumsq).
 // When `dst` is given the samples are ADDED into it (multi-GPU / progressive accumulation),
 // otherwise the result pointer refers to library scratch.

@@ -70,6 +70,9 @@ int ensure_parity_uploaded();  // + the tables only the parity hooks and the A/B
 int bind_device();      // cudaSetDevice(context device): the current device is per host thread, so every entry point
                         // that touches the device calls this first (MCPT_ERR_NO_DEVICE when none is bound)
 
+int pick_chunks(int width, int height, int spp);   // abi_render.cpp: slices per pixel (grid.z)
+int check_cfg(const mcpt_render_cfg* cfg);        // abi_render.cpp: argument checks shared by every render entry point
+
 // No exception crosses the C boundary (include/mcpt.h): every extern "C" body runs inside guarded().
 template <class F>
 int guarded(F&& body) noexcept {

@@ -90,6 +90,7 @@ def lib() -> C.CDLL:
     L.mcpt_cuda_twin_render_cfg.restype = None
     L.mcpt_render_scene.argtypes = [C.POINTER(RenderCfg), _vp, _vp]
     L.mcpt_render_accumulate_device.argtypes = [C.POINTER(RenderCfg), _vp, _vp, _vp]
+    L.mcpt_render_accumulate_device_noalloc.argtypes = [C.POINTER(RenderCfg), _vp, _vp]
     L.mcpt_intersect_batch.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp]
     L.mcpt_intersect_batch_device.argtypes = [_vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp]
     L.mcpt_primary_rays.argtypes = [C.POINTER(RenderCfg), C.c_int, _vp]
@@ -264,6 +265,15 @@ def render_accumulate_device(cfg: RenderCfg, dev_sum_ptr: int, dev_sumsq_ptr: in
     """Adds cfg.spp samples into a caller-owned device float4 buffer (e.g. a torch tensor's data_ptr())."""
     _check(lib().mcpt_render_accumulate_device(C.byref(cfg), _vp(dev_sum_ptr), _vp(dev_sumsq_ptr or None),
                                                _vp(stream or None)))
+
+
+NOALLOC_MAX_SLICE_PIXELS = 1 << 20   # MCPT_NOALLOC_MAX_SLICE_PIXELS
+
+
+def render_accumulate_device_noalloc(cfg: RenderCfg, dev_sum_ptr: int, stream: int = 0) -> None:
+    """render_accumulate_device without any device allocation: fixed 16 MiB static scratch, width*height <= 2**20
+    (include/mcpt.h: mcpt_render_accumulate_device_noalloc)."""
+    _check(lib().mcpt_render_accumulate_device_noalloc(C.byref(cfg), _vp(dev_sum_ptr), _vp(stream or None)))
 
 
 # ---- multi-GPU: spp split + one NCCL reduce behind the C ABI -------------------------------------
