@@ -8,10 +8,12 @@ sys.path.insert(0, ROOT)
 from montecarlopathtracer_b200 import tracer as T, scenes as S
 T.initialize(0)
 T.set_tuning("variant", 511); T.set_tuning("sm_stats", 1)
-for name, eye, spp in (("scene01_lambert", 17.0, 64), ("scene01", 17.0, 64), ("scene02", 23.0, 64), ("scene03", 4.75, 32), ("heightfield:708", 17.0, 16)):
+for name, eye, spp in (("scene01_lambert", 17.0, 64), ("scene01", 17.0, 64), ("scene02", 23.0, 64), ("scene03", 4.75, 32), ("heightfield:708", 17.0, 16), ("heightfield_gpu:708", 17.0, 16)):
     if name.startswith("heightfield"):
         T.load_scene_file(os.path.join(ROOT, "scenes", "scene01_lambert.mcpt"), 1)
-        T.create_geometry(*S.cornell_heightfield(T.get_scene(), 708), 1)
+        T.create_geometry(*S.cornell_heightfield(T.get_scene(), 708), 2 if "gpu" in name else 1)
+        i = T.tree_info()
+        print(f"nodes {i.num_nodes} leaves {i.num_leaves} refs {i.num_leaf_refs} depth {i.max_depth} device MB {i.device_bytes / 1e6:.1f}", flush=True)
     else:
         T.load_scene_file(os.path.join(ROOT, "scenes", name + ".mcpt"), 1)
     print("==", name, flush=True)
