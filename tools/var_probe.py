@@ -14,6 +14,8 @@ args = sys.argv[1:]
 spp, k2spp = 256, 1024
 if "--spp" in args: i = args.index("--spp"); spp = int(args[i + 1]); del args[i:i + 2]
 if "--k2spp" in args: i = args.index("--k2spp"); k2spp = int(args[i + 1]); del args[i:i + 2]
+k4 = "--k4" in args
+if k4: args.remove("--k4")
 variants = [a for a in args]
 EYE = {"scene02": 23.0, "scene03": 4.75}
 
@@ -35,8 +37,13 @@ def render(scene, w, h, n, depth=8):
 
 
 T.initialize(0)
-for scene in ("scene01_lambert", "scene01", "scene02", "scene03"):
-    T.load_scene_file(os.path.join(ROOT, "scenes", scene + ".mcpt"), 1)
+for scene in (("heightfield",) if k4 else ("scene01_lambert", "scene01", "scene02", "scene03")):
+    if k4:   # K4: 1 002 550 triangles, device-built tree, residency automatic (8 blocks per SM) unless a variant carries min_blocks
+        from montecarlopathtracer_b200 import scenes as S
+        T.load_scene_file(os.path.join(ROOT, "scenes", "scene01_lambert.mcpt"), 1)
+        T.create_geometry(*S.cornell_heightfield(T.get_scene(), 708), T.BUILD_GPU)
+    else:
+        T.load_scene_file(os.path.join(ROOT, "scenes", scene + ".mcpt"), 1)
     ref = None
     line = []
     for v in variants:
