@@ -9,10 +9,11 @@ T.initialize(0)
 T.load_scene_file(os.path.join(ROOT, "scenes", "scene01_lambert.mcpt"), T.BUILD_SAH)
 hf = S.cornell_heightfield(T.get_scene(), 708)
 spp = int(sys.argv[1]) if len(sys.argv) > 1 else 64
-cis = [float(x) for x in sys.argv[2:]] or [0.125, 0.25, 0.5, 1.0, 2.0]
+cis = [float(x) for x in sys.argv[2:] if not x.startswith("eb=")] or [0.125, 0.25, 0.5, 1.0, 2.0]
+ebs = [float(x[3:]) for x in sys.argv[2:] if x.startswith("eb=")] or [1.0]
 for mode, name in ((T.BUILD_GPU, "gpu"), (T.BUILD_SAH, "host")):
     for ci in cis:
-        for eb in (1.0,):
+        for eb in ebs:
             T.set_tuning("defaults", 0); T.set_tuning("sah_ci", ci); T.set_tuning("sah_eb", eb)
             T.create_geometry(*hf, mode)
             i = T.tree_info()
