@@ -49,7 +49,7 @@ F_TRI, B_TRI = 71, 40            # Cramer test: 68 flops + 3 divides; three floa
 # the full-size matched-spp renders (tests/golden/fullsize_*.json); only used when the cpu_baseline leg (which measures them
 # live) is switched off.
 ORACLE_WORK = {"K2": "fullsize_K2.json", "K3a": "fullsize_K3a.json", "K3b": "fullsize_K3b.json"}
-KERNEL_SOURCES = ("render_sm.cuh", "render.cuh", "intersect.cuh", "shading.cuh", "launch.cu", "device_scene.h")
+KERNEL_SOURCES = ("render_sm.cuh", "render_pool.cuh", "render.cuh", "intersect.cuh", "shading.cuh", "launch.cu", "device_scene.h")
 
 
 def kernel_source_hash() -> str:

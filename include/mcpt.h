@@ -252,7 +252,7 @@ int mcpt_write_pfm(const char* path, const float* rgb, int width, int height);
 /* ---- tuning / A-B knobs ---------------------------------------------------------------------- */
 /* The library never reads the caller's environment.  Knobs (clamped to their valid range): "shade_threshold",
  * "cam_threshold" [1,32], "tri_cap" [1,64], "chunks" [0,64; 0 = automatic], "sah_ci", "sah_eb" [0.05,100] (next
- * tree build), "leaf_bfs", "sah_resort", "build_timing", "sm_stats", "verify_layout" {0,1}, "min_blocks" {0 = automatic, 4, 5, 6, 8}, "variant", "min_blocks" (MCPT_TUNE builds);
+ * tree build), "leaf_bfs", "sah_resort", "build_timing", "sm_stats", "verify_layout" {0,1}, "min_blocks" {0 = automatic, 4, 5, 6, 8}, "pool" {0, 1: the experimental pooled-lane kernel, csrc/render_pool.cuh}, "variant" (MCPT_TUNE builds);
  * "defaults" restores the shipped configuration.  None of them changes a result beyond fp32 summation order. */
 int mcpt_set_tuning(const char* name, double value);
 int mcpt_get_tuning(const char* name, double* value);

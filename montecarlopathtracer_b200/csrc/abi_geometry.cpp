@@ -175,6 +175,7 @@ int mcpt_initialize(int device) {
         if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail_cuda(e, "cudaEventCreate");
     c.has_device = true;
     c.device = device;
+    cudaDeviceGetAttribute(&c.sm_count, cudaDevAttrMultiProcessorCount, device);
     if (c.has_geometry) return ensure_uploaded();
     return MCPT_OK;
     });
@@ -188,7 +189,7 @@ int mcpt_shutdown(void) {
         cudaSetDevice(c.device);
         release_device_scene(c);
         release_gpu_builder_scratch();
-        c.d_slices.release(); c.d_slices_sq.release(); c.d_sum.release(); c.d_sumsq.release(); c.d_rgb.release();
+        c.d_slices.release(); c.d_slices_sq.release(); c.d_sum.release(); c.d_sumsq.release(); c.d_rgb.release(); c.d_pool.release();
         c.d_frame_seeds.release(); c.d_counter.release(); c.d_rays.release(); c.d_t.release(); c.d_beta.release();
         c.d_gamma.release(); c.d_tri.release();
         for (auto& ev : c.ev) { if (ev) cudaEventDestroy(ev); ev = nullptr; }
@@ -362,6 +363,7 @@ int mcpt_set_tuning(const char* name, double value) {
     else if (k == "tri_cap") t.tri_cap = clampi(1, 64);
     else if (k == "chunks") t.chunks = clampi(0, 64);
     else if (k == "min_blocks") t.min_blocks = clampi(0, 16);
+    else if (k == "pool") t.pool = clampi(0, 1);
     else if (k == "variant") t.variant = clampi(0, 4095);
     else if (k == "leaf_bfs") t.leaf_bfs = clampi(0, 1);
     else if (k == "sah_resort") t.sah_resort = clampi(0, 1);
@@ -388,6 +390,7 @@ int mcpt_get_tuning(const char* name, double* value) {
     else if (k == "tri_cap") *value = t.tri_cap;
     else if (k == "chunks") *value = t.chunks;
     else if (k == "min_blocks") *value = t.min_blocks;
+    else if (k == "pool") *value = t.pool;
     else if (k == "variant") *value = t.variant;
     else if (k == "leaf_bfs") *value = t.leaf_bfs;
     else if (k == "sah_resort") *value = t.sah_resort;

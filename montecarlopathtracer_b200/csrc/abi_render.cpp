@@ -98,6 +98,11 @@ int render_core(const mcpt_render_cfg* cfg, cudaStream_t stream, float4* dst, fl
     r.cam_threshold = std::min(32, std::max(1, tn.cam_threshold));
     r.tri_cap = std::min(64, std::max(1, tn.tri_cap));
     r.min_blocks = tn.min_blocks > 0 ? tn.min_blocks : (c.large_scene ? 8 : 4);   // launch.cu: residency
+    r.pool = 0; r.pool_state = nullptr; r.sm_count = c.sm_count;
+    if (tn.pool > 0 && !moments && !(cfg->flags & (MCPT_FLAG_NEE | MCPT_FLAG_REF_TRAVERSAL | MCPT_FLAG_SIMPLE_KERNEL)) && c.sm_count > 0) {
+        if ((e = c.d_pool.ensure(pool_state_floats(c.sm_count))) != cudaSuccess) return fail_cuda(e, "alloc pool state");
+        r.pool = tn.pool; r.pool_state = c.d_pool.ptr;
+    }
     r.variant = tn.variant;         // MCPT_TUNE builds only
     if (cfg->rng_mode == MCPT_RNG_REFERENCE) {
         // GraphicsRTX.cpp:170-171,192: one draw of uniform_int_distribution<unsigned>(mt19937(1234))

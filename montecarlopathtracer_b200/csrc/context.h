@@ -51,7 +51,8 @@ struct Context {
 
     // render scratch, grown on demand and kept
     DeviceBuffer<float4> d_slices, d_slices_sq, d_sum, d_sumsq;
-    DeviceBuffer<float> d_rgb;
+    DeviceBuffer<float> d_rgb, d_pool;   // d_pool: path state of render_kernel_pool's resident warps
+    int sm_count = 0;
     DeviceBuffer<uint32_t> d_frame_seeds;
     DeviceBuffer<unsigned long long> d_counter;  // >= 4 entries
     // intersect scratch

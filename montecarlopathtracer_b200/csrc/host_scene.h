@@ -44,6 +44,7 @@ struct Tuning {
     int cam_threshold = 16;    // lanes that must need a camera ray before the warp refills its queue  [1, 32]
     int tri_cap = 4;           // triangle tests per lane and round                                    [1, 64]
     int chunks = 0;            // sample slices per tile, 0 = pick_chunks' choice                      [0, 64]
+    int pool = 0;              // 1 = render_kernel_pool (pooled lanes, render_pool.cuh) where it applies; 0 = render_kernel_sm (shipped)
     int min_blocks = 0;        // resident 256-thread blocks per SM: 0 = automatic (4; 8 for scenes that outgrow L2), 4 / 5 / 6 / 8 force it
     int variant = 503;         // MCPT_TUNE builds only: VAR bits of render_kernel_sm
     int leaf_bfs = 0;          // A/B: breadth-first instead of depth-first device order of the leaves

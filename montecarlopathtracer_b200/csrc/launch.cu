@@ -7,6 +7,7 @@
 #include "../../include/mcpt.h"
 #include "hooks.cuh"
 #include "render_sm.cuh"
+#include "render_pool.cuh"
 
 #include <type_traits>
 
@@ -19,6 +20,9 @@
 #endif
 
 namespace mcpt {
+
+constexpr int kPoolBlocksPerSm = 4, kPoolSets = 2;
+size_t pool_state_floats(int sm_count) { return static_cast<size_t>(sm_count) * kPoolBlocksPerSm * 8 * PG_WORDS * 32 * kPoolSets; }
 
 namespace {
 
@@ -59,7 +63,7 @@ cudaError_t launch_render_t(const RenderLaunch& r, cudaStream_t stream) {
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
     p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = 16; p.tri_cap = 4;
-    p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
+    p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter; p.pool_state = nullptr;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
     render_kernel<RNG, KD, NEE, MOMENTS><<<grid, 256, 0, stream>>>(p);
     return cudaGetLastError();
@@ -71,8 +75,17 @@ cudaError_t launch_render_sm_t(const RenderLaunch& r, cudaStream_t stream) {
     p.sc = r.sc; p.cam = r.cam; p.width = r.width; p.height = r.height;
     p.sample_begin = r.sample_begin; p.sample_count = r.sample_count; p.chunks = r.chunks;
     p.depth = r.depth; p.kill_at = r.kill_at; p.gather_at = r.gather_at; p.twin = r.twin; p.seed = r.seed; p.jitter = r.jitter; p.emission_scale = r.emission_scale; p.cam_threshold = r.cam_threshold; p.tri_cap = r.tri_cap;
-    p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter;
+    p.sum = r.slices; p.sumsq = r.slices_sq; p.frame_seeds = r.frame_seeds; p.ray_counter = r.ray_counter; p.pool_state = nullptr;
     dim3 grid((r.width + 15) / 16, (r.height + 15) / 16, r.chunks);
+    // Pooled lanes (render_pool.cuh; mcpt_set_tuning("pool", 1); off by default, profiles/r2_tuning.md): persistent warps,
+    // 64 paths per warp; emission-on-hit estimator without moments.
+    if constexpr (!NEE && !MOMENTS) {
+        if (r.pool > 0 && r.pool_state != nullptr && r.sm_count > 0) {
+            p.pool_state = r.pool_state;
+            render_kernel_pool<RNG, kPoolBlocksPerSm, kPoolSets><<<static_cast<unsigned>(r.sm_count * kPoolBlocksPerSm), 256, 0, stream>>>(p);
+            return cudaGetLastError();
+        }
+    }
 #ifdef MCPT_TUNE
     // tuning build: kernel variants for the headline combination (Philox, no NEE, no moments); 511 = shipped + per-warp
     // round statistics (VAR bit 3).  The round-1 variants (5 ... 375, 128- and 64-thread blocks) were measured and

@@ -24,10 +24,15 @@ struct RenderLaunch {
     bool state_machine;    // render_kernel_sm (warp-voted state machine) instead of render_kernel
     int shade_threshold;   // lanes that must be waiting before the warp leaves the traverse phase
     int min_blocks;        // tuning builds only: 2, 3 or 4 resident 256-thread blocks per SM (register cap 128 / 85 / 64)
+    int pool;              // 1: render_kernel_pool (64 pooled paths per warp; emission-on-hit, no moments); experimental, off by default
+    float* pool_state;     // its scratch: pool_state_floats(sm_count) floats
+    int sm_count;
     int variant;           // tuning builds only: VAR bits of render_kernel_sm
     int cam_threshold;     // camera-ray queue refill threshold (lanes)
     int tri_cap;           // triangle tests per lane and round (VAR bit 6)
 };
+
+size_t pool_state_floats(int sm_count);   // scratch of render_kernel_pool for a device of that many SMs
 
 // Number of kernels launched is returned through *launches (adds to it).
 cudaError_t launch_render(const RenderLaunch& r, cudaStream_t stream, uint32_t* launches);

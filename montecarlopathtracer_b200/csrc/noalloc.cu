@@ -121,6 +121,7 @@ extern "C" int mcpt_render_accumulate_device_noalloc(const mcpt_render_cfg* cfg,
     r.cam_threshold = std::min(32, std::max(1, tn.cam_threshold));
     r.tri_cap = std::min(64, std::max(1, tn.tri_cap));
     r.min_blocks = tn.min_blocks > 0 ? tn.min_blocks : (c.large_scene ? 8 : 4);
+    r.pool = 0; r.pool_state = nullptr; r.sm_count = 0;   // the pooled kernel's scratch is cudaMalloc'ed: not on this path
     r.variant = tn.variant;
 
     c.counters.launches = 0;

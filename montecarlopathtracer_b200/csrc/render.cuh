@@ -32,6 +32,7 @@ struct RenderParams {
     float4* sumsq;         // same layout, or nullptr
     const uint32_t* frame_seeds;  // reference stream: one seed per sample of this launch
     unsigned long long* ray_counter;
+    float* pool_state;     // render_kernel_pool: per resident warp, PG_WORDS x (32 * SETS) words of path state (stays in L2)
 };
 
 // rtx.hlsl:384-398.  EXACT: the shader's expressions with IEEE divides and square root (primary_rays_kernel: rays

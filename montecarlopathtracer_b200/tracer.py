@@ -413,7 +413,7 @@ def get_tuning(name: str) -> float:
 
 _ENV_KNOBS = {"MCPT_SM_SHADE": "shade_threshold", "MCPT_SM_CAMR": "cam_threshold", "MCPT_SM_TRICAP": "tri_cap", "MCPT_CHUNKS": "chunks",
               "MCPT_SM_MINBLOCKS": "min_blocks", "MCPT_SM_VARIANT": "variant", "MCPT_SAH_CI": "sah_ci", "MCPT_SAH_EB": "sah_eb",
-              "MCPT_LEAF_BFS": "leaf_bfs", "MCPT_SAH_RESORT": "sah_resort", "MCPT_BUILD_TIMING": "build_timing", "MCPT_SM_STATS": "sm_stats"}
+              "MCPT_LEAF_BFS": "leaf_bfs", "MCPT_SAH_RESORT": "sah_resort", "MCPT_BUILD_TIMING": "build_timing", "MCPT_SM_STATS": "sm_stats", "MCPT_POOL": "pool"}
 
 
 def tuning_from_env() -> dict:

@@ -278,6 +278,34 @@ def test_kernel_variants_render_identical_images(gpu, scenes, flags):
     assert imgs[0].max() > 0
 
 
+@pytest.mark.parametrize("name,ez", [("scene01_lambert", 17.0), ("scene02", 23.0), ("scene03", 4.75)])
+def test_pooled_lane_kernel_renders_the_same_image(gpu, scenes, name, ez):
+    """render_kernel_pool (mcpt_set_tuning("pool", 1); experimental, off by default): 64 pooled paths per persistent warp,
+    same rays, same arithmetic, same per-slice sums as render_kernel_sm.  Bit-identical images and ray counts on scene01 /
+    scene02 in both random streams and for ragged sizes and odd slice counts; on scene03 (glass + sharp Phong) the compiler
+    contracts a few shading expressions differently in the two kernels, a handful of paths per million take another
+    turn: stated as a bound."""
+    T = gpu
+    _load(T, scenes[name], T.BUILD_SAH)
+    try:
+        for (w, h, spp, depth, chunks, kw) in ((203, 121, 24, 8, 0, {}), (96, 64, 9, 5, 3, {}), (64, 48, 6, 8, 2, dict(rng_mode=T.RNG_REFERENCE)),
+                                               (160, 100, 4, 5, 1, {})):
+            out = []
+            for pool in (0, 1):
+                T.set_tuning("defaults", 0); T.set_tuning("pool", pool); T.set_tuning("chunks", chunks)
+                img = T.render_scene(T.render_cfg(w, h, spp, depth, seed=3, eye=(0, 5, ez), at=(0, 5, ez - 1), **kw))
+                out.append((img, T.counters().rays))
+            (a, ra), (b, rb) = out
+            assert a.max() > 0
+            if name == "scene03":
+                assert (a != b).any(-1).mean() < 1e-3 and abs(ra - rb) <= 1e-5 * ra + 8
+                assert np.isclose(a.mean(), b.mean(), rtol=2e-3)
+            else:
+                assert np.array_equal(a, b) and ra == rb
+    finally:
+        T.set_tuning("defaults", 0)
+
+
 def test_render_ragged_sizes(gpu, oracle, scenes):
     """Sizes that are not multiples of the 16x16 block tile or of 32 (the reference drops such edge
     pixels, GraphicsRTX.cpp:209), 1x1, and a single sample."""
