@@ -102,6 +102,7 @@ int ensure_parity_uploaded() {
     Context& c = ctx();
     if (const int rc = ensure_uploaded()) return rc;
     if (c.parity_uploaded) return MCPT_OK;
+    pack_parity_tables(c.tree, c.packed);
     cudaError_t e;
     if ((e = upload(c.d_ref_nodes, c.packed.ref_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload ref_nodes");
     if ((e = upload(c.d_kd_nodes, c.packed.kd_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload kd_nodes");

@@ -28,58 +28,47 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     // Device order of the leaves: depth first (left subtree first), so that the id lists, triangle records and
     // headers of spatially neighbouring leaves are neighbours in memory (the host tree keeps the reference's
     // breadth-first leaf order).  Matters once the scene outgrows L1/L2 (K4: L2 hit rate, DRAM page locality).
+    // A leaf's depth-first ordinal is the number of leaves to its left: children are numbered after their parents
+    // (breadth-first tree), so one backward pass counts the leaves and references under every node and one forward
+    // pass hands each child its start -- two flat array passes instead of a stack walk that appends ids one by one.
     out.leaf_order.assign(nN, 0xFFFFFFFFu);
     std::vector<uint32_t> devOffset(nN, 0u);
-    out.leaf_ids.clear();
-    out.leaf_ids.reserve(tree.leaf_ids.size() + 1);
-    {
-        std::vector<uint32_t> todo(1, 0u);
-        uint32_t ordinal = 0;
-        if (tuning().leaf_bfs) {  // A/B knob: keep the breadth-first leaf order
-            todo.clear();
-            for (uint32_t k = 0; k < nN; ++k)
-                if (tree.split_axis[k] == 0) {
-                    out.leaf_order[k] = ordinal++;
-                    devOffset[k] = static_cast<uint32_t>(out.leaf_ids.size());
-                    for (uint32_t i = 0; i < tree.leaf_count[k]; ++i) out.leaf_ids.push_back(tree.leaf_ids[tree.leaf_offset[k] + i]);
-                }
+    size_t totalRefs = 0;
+    if (tuning().leaf_bfs) {  // A/B knob: keep the breadth-first leaf order
+        uint32_t ordinal = 0, off = 0;
+        for (uint32_t k = 0; k < nN; ++k)
+            if (tree.split_axis[k] == 0) { out.leaf_order[k] = ordinal++; devOffset[k] = off; off += tree.leaf_count[k]; }
+        totalRefs = off;
+    } else {
+        std::vector<uint32_t> leavesUnder(nN), refsUnder(nN);
+        for (size_t k = nN; k-- > 0;) {
+            if (tree.split_axis[k] == 0) { leavesUnder[k] = 1u; refsUnder[k] = tree.leaf_count[k]; }
+            else { const uint32_t L = tree.left[k]; leavesUnder[k] = leavesUnder[L] + leavesUnder[L + 1]; refsUnder[k] = refsUnder[L] + refsUnder[L + 1]; }
         }
-        while (!todo.empty()) {
-            const uint32_t k = todo.back();
-            todo.pop_back();
-            if (tree.split_axis[k] != 0) {
-                todo.push_back(tree.left[k] + 1u);
-                todo.push_back(tree.left[k]);
-            } else {
-                out.leaf_order[k] = ordinal++;
-                devOffset[k] = static_cast<uint32_t>(out.leaf_ids.size());
-                for (uint32_t i = 0; i < tree.leaf_count[k]; ++i) out.leaf_ids.push_back(tree.leaf_ids[tree.leaf_offset[k] + i]);
-            }
+        std::vector<uint32_t> firstLeaf(nN, 0u);
+        for (size_t k = 0; k < nN; ++k) {
+            if (tree.split_axis[k] == 0) { out.leaf_order[k] = firstLeaf[k]; continue; }
+            const uint32_t L = tree.left[k];
+            firstLeaf[L] = firstLeaf[k]; devOffset[L] = devOffset[k];
+            firstLeaf[L + 1] = firstLeaf[k] + leavesUnder[L]; devOffset[L + 1] = devOffset[k] + refsUnder[L];
         }
+        totalRefs = nN ? refsUnder[0] : 0;
     }
+    out.leaf_ids.assign(totalRefs ? totalRefs : 1, 0u);
+#pragma omp parallel for schedule(static) if (nN > 65536)
+    for (size_t k = 0; k < nN; ++k)
+        if (tree.split_axis[k] == 0)
+            for (uint32_t i = 0; i < tree.leaf_count[k]; ++i) out.leaf_ids[devOffset[k] + i] = tree.leaf_ids[tree.leaf_offset[k] + i];
     lap("leaf order (depth first)");
-    out.ref_nodes.resize(2 * nN);
+    // Parity-only tables (reference-order boxes, per-reference record copies) are built on first use: pack_parity_tables.
+    out.ref_nodes.clear();
+    out.leaf_tris.clear();
     out.kd_nodes.resize(nN);
 #pragma omp parallel for schedule(static) if (nN > 65536)
     for (size_t k = 0; k < nN; ++k) {
-        const float* bb = &tree.aabb[6 * k];
-        uint32_t a, b, kx, ky;
-        if (tree.split_axis[k] != 0) {
-            a = tree.left[k];
-            b = 0u;
-            kx = as_uint(tree.split_value[k]);
-            ky = (tree.left[k] << 2) | (tree.split_axis[k] - 1u);
-        } else {
-            a = devOffset[k];
-            b = 0x80000000u | tree.leaf_count[k];
-            kx = devOffset[k];
-            ky = (tree.leaf_count[k] << 2) | 3u;
-        }
-        out.ref_nodes[2 * k] = make_float4(bb[0], bb[1], bb[2], as_float(a));
-        out.ref_nodes[2 * k + 1] = make_float4(bb[3], bb[4], bb[5], as_float(b));
-        out.kd_nodes[k] = make_uint2(kx, ky);
+        if (tree.split_axis[k] != 0) out.kd_nodes[k] = make_uint2(as_uint(tree.split_value[k]), (tree.left[k] << 2) | (tree.split_axis[k] - 1u));
+        else out.kd_nodes[k] = make_uint2(devOffset[k], (tree.leaf_count[k] << 2) | 3u);
     }
-    if (out.leaf_ids.empty()) out.leaf_ids.push_back(0u);
     for (int i = 0; i < 3; ++i) { out.bmin[i] = tree.aabb[i]; out.bmax[i] = tree.aabb[3 + i]; }
 
     lap("node tables");
@@ -128,12 +117,6 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         }
     }
     lap("emitters");
-    out.leaf_tris.resize(3 * out.leaf_ids.size());
-#pragma omp parallel for schedule(static) if (out.leaf_ids.size() > 65536)
-    for (size_t k = 0; k < out.leaf_ids.size(); ++k)
-        for (int j = 0; j < 3; ++j) out.leaf_tris[3 * k + j] = out.tri_isect[3 * static_cast<size_t>(out.leaf_ids[k]) + j];
-
-    lap("leaf records");
     const bool ropesOk = build_ropes(tree, out);
     lap("neighbour links + leaf blocks");
 
@@ -154,6 +137,27 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         out.mats[3 * m + 2] = make_float4(p[6], p[7], p[8], p[11]);  // Ks, Ni
     }
     return ropesOk;
+}
+
+// The tables only the parity hooks and the A/B kernels read: the reference-order boxes (ref_nodes) and the per-reference
+// copies of the triangle records (leaf_tris).  Built on their first use (ensure_parity_uploaded, check_ropes' callers):
+// at 1 M triangles they are 130 MB that a render never touches.
+void pack_parity_tables(const HostTree& tree, PackedScene& out) {
+    const size_t nN = tree.num_nodes();
+    if (out.ref_nodes.size() == 2 * nN && out.leaf_tris.size() == 3 * out.leaf_ids.size()) return;
+    out.ref_nodes.resize(2 * nN);
+#pragma omp parallel for schedule(static) if (nN > 65536)
+    for (size_t k = 0; k < nN; ++k) {
+        const float* bb = &tree.aabb[6 * k];
+        const bool inner = tree.split_axis[k] != 0;
+        const uint32_t a = inner ? tree.left[k] : out.kd_nodes[k].x, b = inner ? 0u : (0x80000000u | tree.leaf_count[k]);
+        out.ref_nodes[2 * k] = make_float4(bb[0], bb[1], bb[2], as_float(a));
+        out.ref_nodes[2 * k + 1] = make_float4(bb[3], bb[4], bb[5], as_float(b));
+    }
+    out.leaf_tris.resize(3 * out.leaf_ids.size());
+#pragma omp parallel for schedule(static) if (out.leaf_ids.size() > 65536)
+    for (size_t k = 0; k < out.leaf_ids.size(); ++k)
+        for (int j = 0; j < 3; ++j) out.leaf_tris[3 * k + j] = out.tri_isect[3 * static_cast<size_t>(out.leaf_ids[k]) + j];
 }
 
 // D3DXMatrixLookAtRH / Inverse / PerspectiveFovRH in closed form (GraphicsRTX.cpp:173-184):

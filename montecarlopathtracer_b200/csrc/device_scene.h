@@ -74,7 +74,8 @@ struct PackedScene {
 };
 
 bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out);  // false: scene too large for the leaf-block layout
-bool build_ropes(const HostTree& tree, PackedScene& out);  // kd_ropes.cpp; needs kd_nodes, leaf_tris of pack_scene; false: too many leaf references
+void pack_parity_tables(const HostTree& tree, PackedScene& out);  // ref_nodes, leaf_tris: built on first use (parity hooks, A/B kernels)
+bool build_ropes(const HostTree& tree, PackedScene& out);  // kd_ropes.cpp; needs kd_nodes, leaf_ids, tri_isect of pack_scene; false: too many leaf references
 bool check_ropes(const HostTree& tree, const PackedScene& packed, std::string& err);  // kd_ropes.cpp: structural check of leaf_blob / rope_nodes
 int walk_ropes_host(const PackedScene& packed, const float ray[6], int maxHops, uint32_t* leafOff, float* exitT, uint32_t* exitAxis);  // kd_ropes.cpp: diagnostic mirror of the walk
 DCamera make_camera(const float eye[3], const float at[3], const float up[3], float fovy, int width, int height, int twin = 0);

@@ -13,7 +13,7 @@
 //
 //   leaf_blob   one block per leaf, leaves in depth-first order: 4 x float4 of header
 //               {cell.lo, first slot in leaf_ids} {cell.hi, count} {rope -x, +x, -y, +y} {rope -z, +z, -, -}
-//               followed by the leaf's `count` triangle records (3 x float4 each, the leaf_tris records).  A leaf is
+//               followed by the leaf's `count` triangle records (3 x float4 each, the tri_isect records of its ids).  A leaf is
 //               named by its HANDLE: bits 0-27 = offset of the block in float4 units, bits 28-30 = min(count, 7).
 //               With the handle alone a ray knows where the triangle records are and (for all but leaves of 7+
 //               triangles) how many: the triangle tests do not wait for the header, which is only needed for the
@@ -41,6 +41,12 @@ struct Cell {
     float lo[3], hi[3];
 };
 
+// What a node hands its children: its cell and, per face, the deepest node covering that face from the other side.
+struct NodeCtx {
+    Cell cell;
+    uint32_t rope[6];
+};
+
 struct Builder {
     const HostTree& t;
     PackedScene& out;
@@ -61,45 +67,56 @@ struct Builder {
         return r;
     }
 
-    void walk(uint32_t node, const Cell& cell, const uint32_t ropes[6], int depth = 0) {
-        if (t.split_axis[node] == 0) {
-            float4* blk = out.leaf_blob.data() + (leafHandle[node] & kLeafOffsetMask);
-            const uint32_t first = out.kd_nodes[node].x, count = t.leaf_count[node];
-            blk[0] = make_float4(cell.lo[0], cell.lo[1], cell.lo[2], as_float(first));
-            blk[1] = make_float4(cell.hi[0], cell.hi[1], cell.hi[2], as_float(count));
-            uint32_t enc[6];
-            for (int f = 0; f < 6; ++f) {
-                const uint32_t r = ropes[f];
-                enc[f] = (r != kNone && t.split_axis[r] == 0) ? (kRopeIsLeaf | leafHandle[r]) : r;
-            }
-            blk[2] = make_float4(as_float(enc[0]), as_float(enc[1]), as_float(enc[2]), as_float(enc[3]));
-            blk[3] = make_float4(as_float(enc[4]), as_float(enc[5]), 0.0f, 0.0f);
-            for (uint32_t k = 0; k < 3 * count; ++k) blk[4 + k] = out.leaf_tris[3 * static_cast<size_t>(first) + k];
-            return;
+    // A leaf's block: header {cell.lo, first} {cell.hi, count} {ropes} + its triangle records, read from tri_isect through
+    // the leaf's id list (the record of leaf_ids[first + i] with the triangle id in its free lane).
+    void write_leaf(uint32_t node, const NodeCtx& c) {
+        float4* blk = out.leaf_blob.data() + (leafHandle[node] & kLeafOffsetMask);
+        const uint32_t first = out.kd_nodes[node].x, count = t.leaf_count[node];
+        blk[0] = make_float4(c.cell.lo[0], c.cell.lo[1], c.cell.lo[2], as_float(first));
+        blk[1] = make_float4(c.cell.hi[0], c.cell.hi[1], c.cell.hi[2], as_float(count));
+        uint32_t enc[6];
+        for (int f = 0; f < 6; ++f) {
+            const uint32_t r = c.rope[f];
+            enc[f] = (r != kNone && t.split_axis[r] == 0) ? (kRopeIsLeaf | leafHandle[r]) : r;
         }
+        blk[2] = make_float4(as_float(enc[0]), as_float(enc[1]), as_float(enc[2]), as_float(enc[3]));
+        blk[3] = make_float4(as_float(enc[4]), as_float(enc[5]), 0.0f, 0.0f);
+        for (uint32_t i = 0; i < count; ++i) {
+            const float4* rec = out.tri_isect.data() + 3 * static_cast<size_t>(out.leaf_ids[first + i]);
+            blk[4 + 3 * i] = rec[0]; blk[5 + 3 * i] = rec[1]; blk[6 + 3 * i] = rec[2];
+        }
+    }
+    void split(uint32_t node, const NodeCtx& c, NodeCtx& l, NodeCtx& r) const {
         const int a = static_cast<int>(t.split_axis[node]) - 1;
         const float s = t.split_value[node];
         const uint32_t L = t.left[node], R = L + 1;
-        Cell cl = cell, cr = cell;
-        cl.hi[a] = s;
-        cr.lo[a] = s;
-        uint32_t rl[6], rr[6];
-        for (int f = 0; f < 6; ++f) { rl[f] = ropes[f]; rr[f] = ropes[f]; }
-        rl[2 * a + 1] = R;
-        rr[2 * a] = L;
+        l = c; r = c;
+        l.cell.hi[a] = s;
+        r.cell.lo[a] = s;
+        l.rope[2 * a + 1] = R;
+        r.rope[2 * a] = L;
         for (int f = 0; f < 6; ++f) {
-            rl[f] = tighten(rl[f], f >> 1, (f & 1) != 0, cl);
-            rr[f] = tighten(rr[f], f >> 1, (f & 1) != 0, cr);
+            l.rope[f] = tighten(l.rope[f], f >> 1, (f & 1) != 0, l.cell);
+            r.rope[f] = tighten(r.rope[f], f >> 1, (f & 1) != 0, r.cell);
         }
-        // subtrees write disjoint leaf blocks: the upper levels fan out as tasks (build_ropes opens the parallel region)
+    }
+
+    // Depth first, the upper levels fanned out as tasks: subtrees write disjoint, CONTIGUOUS runs of leaf blocks (the blocks
+    // are laid out in depth-first leaf order), which is why this beats a level-synchronous sweep whose leaves of one depth
+    // are scattered over the whole blob (measured at 1 M triangles: 150 ms against 250 ms on 8 cores).
+    void walk(uint32_t node, const NodeCtx& c, int depth = 0) {
+        if (t.split_axis[node] == 0) { write_leaf(node, c); return; }
+        NodeCtx l, r;
+        split(node, c, l, r);
+        const uint32_t L = t.left[node];
         if (depth < 7) {
-#pragma omp task firstprivate(L, cl, rl, depth)
-            walk(L, cl, rl, depth + 1);
-            walk(R, cr, rr, depth + 1);
+#pragma omp task firstprivate(L, l, depth)
+            walk(L, l, depth + 1);
+            walk(L + 1, r, depth + 1);
 #pragma omp taskwait
         } else {
-            walk(L, cl, rl, depth + 1);
-            walk(R, cr, rr, depth + 1);
+            walk(L, l, depth + 1);
+            walk(L + 1, r, depth + 1);
         }
     }
 };
@@ -127,18 +144,18 @@ bool build_ropes(const HostTree& tree, PackedScene& out) {
     }
     // three float4 of padding: a lane may read one record past a leaf of 7+ triangles' known count, never past this
     out.leaf_blob.assign(units + 3, make_float4(0, 0, 0, 0));
-    Cell root;
-    for (int i = 0; i < 3; ++i) { root.lo[i] = tree.aabb[i]; root.hi[i] = tree.aabb[3 + i]; }
-    const uint32_t none[6] = {kNone, kNone, kNone, kNone, kNone, kNone};
+    NodeCtx root;
+    for (int i = 0; i < 3; ++i) { root.cell.lo[i] = tree.aabb[i]; root.cell.hi[i] = tree.aabb[3 + i]; }
+    for (int f = 0; f < 6; ++f) root.rope[f] = kNone;
 #pragma omp parallel
 #pragma omp single
-    b.walk(0u, root, none);
+    b.walk(0u, root);
     return true;
 }
 
 // Structural check of what build_ropes produced (host only; mcpt_check_stackless_layout, CPU tests):
 //   * the blocks follow each other in leaf order, every handle carries its block's offset and min(count, 7), the
-//     header repeats the tree's first/count and the records are the leaf_tris records of that leaf;
+//     header repeats the tree's first/count and the records are the tri_isect records of the leaf's id list;
 //   * for every leaf and face: a missing rope only where the face lies on the scene box; otherwise the rope's cell touches the face
 //     from the other side and covers it in the two other axes (so the cell behind any exit point is below the rope),
 //     a leaf rope names a real leaf, and a node rope is the deepest possible (its plane cuts the face).
@@ -174,7 +191,8 @@ bool check_ropes(const HostTree& t, const PackedScene& out, std::string& err) {
             const float lo = i == 0 ? blk[0].x : (i == 1 ? blk[0].y : blk[0].z), hi = i == 0 ? blk[1].x : (i == 1 ? blk[1].y : blk[1].z);
             if (lo != cell[k].lo[i] || hi != cell[k].hi[i]) { err = "leaf cell of node " + std::to_string(k); return false; }
         }
-        if (std::memcmp(blk + 4, out.leaf_tris.data() + 3 * static_cast<size_t>(out.kd_nodes[k].x), 48 * static_cast<size_t>(count)) != 0) { err = "leaf records of node " + std::to_string(k); return false; }
+        for (uint32_t i = 0; i < count; ++i)
+            if (std::memcmp(blk + 4 + 3 * i, out.tri_isect.data() + 3 * static_cast<size_t>(out.leaf_ids[out.kd_nodes[k].x + i]), 48) != 0) { err = "leaf records of node " + std::to_string(k); return false; }
         if (nodeOfOffset.size() <= units) nodeOfOffset.resize(units + 1, kNone);
         nodeOfOffset[units] = k;
         units += 4 + 3 * static_cast<size_t>(count);
