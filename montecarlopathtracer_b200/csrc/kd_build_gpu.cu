@@ -371,11 +371,13 @@ void release_gpu_builder_scratch() {
     g_arena = Arena();
 }
 
-// Needs a bound CUDA device (the caller checks).  false + err: not enough room for this scene's duplication or a CUDA error.
-bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
+namespace {
+// One attempt with room for `dup` references per triangle.  false + err: a CUDA error, or (tooSmall) the scene duplicates more
+// than that -- the caller retries with more room.
+bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err, size_t dup, bool& tooSmall) {
     const auto t0 = std::chrono::steady_clock::now();
     const uint32_t nT = static_cast<uint32_t>(scene.num_triangles());
-    const size_t refCap = 6ull * nT + 4096, nodeCap = 8ull * nT + 4096;
+    const size_t refCap = dup * nT + 4096, nodeCap = (dup + 2) * nT + 4096;
     const float ci = tuning().sah_ci;
     const int maxDepth = std::min(31, static_cast<int>(8.0 + 1.3 * std::log2(static_cast<double>(std::max<uint32_t>(nT, 1)))));
     cudaStream_t s = nullptr;
@@ -427,7 +429,7 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
     for (int depth = 0; nNodes > 0; ++depth) {
         depthReached = static_cast<uint32_t>(depth);
         const int nxt = cur ^ 1;
-        if (static_cast<size_t>(levelBase) + nNodes > nodeCap) { err = "GPU KD build: node capacity exceeded"; return false; }
+        if (static_cast<size_t>(levelBase) + nNodes > nodeCap) { err = "GPU KD build: node capacity exceeded"; tooSmall = true; return false; }
         // scan sizes include one extra element so that the last entry of each exclusive sum is the level's total
         GK_CHECK(cudaMemsetAsync(nL.p, 0, (nNodes + 1) * 4, s)); GK_CHECK(cudaMemsetAsync(nR.p, 0, (nNodes + 1) * 4, s));
         GK_CHECK(cudaMemsetAsync(leafCursor.p, 0, (nNodes + 1) * 4, s));
@@ -438,7 +440,7 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
         uint32_t numBig = 0;
         GK_CHECK(cudaMemcpyAsync(&numBig, bigRank.p + nNodes, 4, cudaMemcpyDeviceToHost, s));
         GK_CHECK(cudaStreamSynchronize(s));
-        if (numBig > maxBig) { err = "GPU KD build: histogram capacity exceeded"; return false; }
+        if (numBig > maxBig) { err = "GPU KD build: histogram capacity exceeded"; tooSmall = true; return false; }
         if (numBig) {
             GK_CHECK(cudaMemsetAsync(bins.p, 0, static_cast<size_t>(numBig) * 3 * 2 * kBins * 4, s));
             bin_kernel<<<grid(nRefs), B, 0, s>>>(level[cur].p, refTri[cur].p, refNode[cur].p, nRefs, triLo.p, triHi.p, binSlot.p, bins.p);
@@ -462,7 +464,8 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
         GK_CHECK(cudaStreamSynchronize(s));
         const uint32_t numSplit = tot[0], nextRefs = tot[1], levelLeafRefs = tot[2];
         if (nextRefs > refCap || static_cast<size_t>(leafIdBase) + levelLeafRefs > refCap || 2ull * numSplit > 2 * levelCap) {
-            err = "GPU KD build: reference capacity exceeded (duplication above 6x)";
+            err = "GPU KD build: reference capacity exceeded (duplication above " + std::to_string(dup) + "x)";
+            tooSmall = true;
             return false;
         }
         const uint32_t nextBase = levelBase + nNodes;
@@ -503,6 +506,24 @@ bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
                      leafIdBase, depthReached, out.build_seconds, sec(t0, tAlloc), sec(tAlloc, tLevels), sec(tLevels, std::chrono::steady_clock::now()));
     }
     return true;
+}
+}  // namespace
+
+// Needs a bound CUDA device (the caller checks).  The scratch is sized for 6 references per triangle (tessellated surfaces
+// duplicate 1.3-2.5x); a scene that duplicates more -- a soup of large overlapping triangles -- is built again with room for
+// 16x, 40x, 100x.  false + err: beyond that, out of device memory, or a CUDA error.
+bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
+    const auto t0 = std::chrono::steady_clock::now();
+    for (const size_t dup : {6u, 16u, 40u, 100u}) {
+        bool tooSmall = false;
+        if (build_gpu_tree_with(scene, out, err, dup, tooSmall)) {
+            out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();   // retries included
+            return true;
+        }
+        cudaGetLastError();
+        if (!tooSmall) return false;
+    }
+    return false;
 }
 
 }  // namespace mcpt
