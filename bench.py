@@ -373,6 +373,21 @@ def roofline(T, m, nn, nt, clocks, peaks, workload):
     return r
 
 
+def ncu_view(workload, m, peaks):
+    """What only ncu can tell about a workload's render kernel (profiles/ncu_constants.json, keyed by the kernel-source hash; None
+    for any other kernel) next to this run's own launch time: achieved DRAM GB/s against the measured HBM peak, cache hit rates,
+    SIMT efficiency, issue-slot use.  For K4 -- the one workload whose scene outgrows the caches -- this is the memory-side figure."""
+    nc = ncu_constants(workload)
+    if not nc:
+        return None
+    t = m["_t_launch"]
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    return {"source": nc["source"], "kernel_source_hash": nc["kernel_source_hash"], "dram_bytes_per_launch": nc["dram_bytes_per_launch"],
+            "dram_gbs": nc["dram_bytes_per_launch"] / t / 1e9, "hbm_peak_gbs": hbm_peak, "hbm_frac": nc["dram_bytes_per_launch"] / t / 1e9 / hbm_peak,
+            "l1_hit_rate": nc["l1_hit_rate"], "l2_hit_rate": nc["l2_hit_rate"], "warp_inst_per_ray": nc["warp_inst_per_ray"],
+            "threads_per_inst": nc["threads_per_inst"], "issue_slots_busy": nc["issue_slots_busy"], "registers_per_thread": nc["registers_per_thread"]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -431,6 +446,11 @@ def main():
     main_inner = 100 if args.workload == "K1" else 1
     m = B.run(args.workload, args.steps, args.warmup, max(1, min(args.steps, 3)), build_mode, flags, args.scaling, args.spp, inner=main_inner)
 
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
     extras = {}
     if not args.no_extras and args.workload == "K2" and not args.spp:
         if world == 1:
@@ -438,6 +458,7 @@ def main():
             for w, inner in (("K1", 100), ("K3a", 1), ("K3b", 1), ("K4", 1)):
                 o = B.run(w, 2, 1, 2 if w == "K4" else 1, mode_for(w), flags, "weak", inner=inner)
                 o["tree"] = tree_name[mode_for(w)]
+                o["ncu"] = ncu_view(w, o, peaks)
                 others.append({k: v for k, v in o.items() if not k.startswith("_")})
             extras["other_workloads"] = others
         else:
@@ -490,11 +511,7 @@ def main():
         except OSError:
             pass
     line["cpu_baseline"] = cpu
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except OSError:
-        pass
+    line["ncu"] = ncu_view(args.workload, m, peaks)
     line["roofline"] = roofline(T, m, nn, nt, m["clocks"], peaks, args.workload) if nn is not None else None
     line.update(extras)
     if sampler:
