@@ -477,15 +477,18 @@ void build_sah_tree(const HostScene& scene, HostTree& out) {
     nodes.reserve(6 * nT + 1024);
     nodes.emplace_back();
     nodes[0].cell = root;
+    // Small scenes are built by the calling thread alone: waking a team of 16-24 threads costs more than the 862-triangle
+    // Cornell box takes to build (K1's end-to-end step is 2.7 ms of rendering).
+    const bool team = nT > 4096;
     if (tuning().sah_resort) {  // A/B knob: the re-sorting builder on every level
-#pragma omp parallel
+#pragma omp parallel if (team)
 #pragma omp single
         build_node(scene, nodes, 0, refs, 0, maxDepth);
     } else {
         std::vector<SEvent> ev[3];
         for (int axis = 0; axis < 3; ++axis) ev[axis].reserve(2 * nT);
         for (size_t t = 0; t < nT; ++t) push_ref_events(ev, refs[t], static_cast<uint32_t>(t));
-#pragma omp parallel
+#pragma omp parallel if (team)
 #pragma omp single
         {
 #pragma omp taskgroup

@@ -147,7 +147,7 @@ bool build_ropes(const HostTree& tree, PackedScene& out) {
     NodeCtx root;
     for (int i = 0; i < 3; ++i) { root.cell.lo[i] = tree.aabb[i]; root.cell.hi[i] = tree.aabb[3 + i]; }
     for (int f = 0; f < 6; ++f) root.rope[f] = kNone;
-#pragma omp parallel
+#pragma omp parallel if (nN > 8192)
 #pragma omp single
     b.walk(0u, root);
     return true;
