@@ -332,9 +332,14 @@ class Bench:
         torch.cuda.synchronize()
         e2e_s, = self.allmax(time.perf_counter() - ta)
         k = e2e_steps * inner
-        out["e2e"] = {"value": float(W) * H * total_spp * k / e2e_s / 1e6, "unit": "Mpaths/s", "h2d_bytes_per_step": int(info.device_bytes),
+        # host -> device per step: with the device builder the caller's tables go up and everything else is made there; with a host
+        # builder the packed render-path tables go up
+        device_made = build_mode == T.BUILD_GPU and T.get_tuning("device_pack") != 0
+        h2d = int(v.nbytes + n.nbytes + tr.nbytes + m.nbytes) if device_made else int(info.device_bytes)
+        out["e2e"] = {"value": float(W) * H * total_spp * k / e2e_s / 1e6, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d,
+                      "h2d_what": "the caller's scene tables (tree and render-path tables are built on the device)" if device_made else "packed render-path tables (built on the host)",
                       "d2h_bytes_per_step": W * H * 3 * 4, "steps": e2e_steps, "timer": "host wall clock (perf_counter) around blocking C-ABI calls, max over ranks",
-                      "includes": "mcpt_create_geometry (host KD build + pack + H2D) and mcpt_render_scene_distributed (render, ncclReduce, D2H of the float3 image) every step",
+                      "includes": "mcpt_create_geometry (KD build + pack + H2D) and mcpt_render_scene_distributed (render, ncclReduce, D2H of the float3 image) every step",
                       "split_ms_per_render": {a: b / k for a, b in split.items()}}
         out["e2e"]["split_ms_per_render"]["pack_and_upload_ms"] = out["e2e"]["split_ms_per_render"]["create_geometry_ms"] - out["e2e"]["split_ms_per_render"]["kd_build_ms"]
         out["first_load_s"] = t_geo

@@ -42,7 +42,8 @@ enum {
     MCPT_BUILD_REFERENCE = 0, /* node-for-node the tree of KDTree.hpp:58-287 (parity anchor) */
     MCPT_BUILD_SAH = 1,       /* this library's own O(n log n) SAH builder on the host (same hits, other tree) */
     MCPT_BUILD_GPU = 2        /* level-synchronous SAH build on the bound device (binned above 32 references per node, exact
-                                 below): the fast ingest for large scenes (1 M triangles: ~15x the host builder); needs mcpt_initialize */
+                                 below) AND the render-path tables made there too (leaf blocks, neighbour links, shading records:
+                                 nothing packed on the host, nothing uploaded): the fast ingest for large scenes; needs mcpt_initialize */
 };
 
 /* Which OBJ/MTL reader semantics mcpt_load_obj follows. */
@@ -131,7 +132,7 @@ typedef struct mcpt_tree_info {
     int32_t num_nodes, num_leaves, num_leaf_refs, max_depth;
     int32_t num_emitter_triangles;
     double build_seconds;
-    uint64_t device_bytes;   /* nodes + ids + triangle records resident in HBM */
+    uint64_t device_bytes;   /* tables resident in HBM: what a render reads, plus the parity-only tables once a hook asked for them */
 } mcpt_tree_info;
 
 /* ---- PW::Tracer::Initialize (CUTracer.cu:220-223) ---------------------------------------- */
@@ -150,6 +151,10 @@ int mcpt_get_tree_info(mcpt_tree_info* info);
  * handles, neighbour links: csrc/kd_ropes.cpp check_ropes); needs no device.  MCPT_OK, or MCPT_ERR_INTERNAL with the
  * first inconsistency in mcpt_last_error(). */
 int mcpt_check_stackless_layout(void);
+/* Diagnostic: the render-path tables resident on the device (leaf blocks, location nodes, shading records) against the host's own
+ * pack of the same tree, word for word; differing = {leaf-block float4s, nodes, shading float4s}.  After MCPT_BUILD_GPU this
+ * compares what the device pack made with what pack_scene + build_ropes make on the host (must be {0, 0, 0}). */
+int mcpt_debug_compare_device_tables(uint64_t differing[3]);
 /* Diagnostic, host only: the leaves (block offsets in float4 units) the stackless walk visits for one ray {origin, direction},
  * with each leaf's exit distance and axis, and the triangle ids those leaves hold (0xFFFFFFFF between leaves).  Mirrors the
  * WALK of the device code operation for operation; it tests no triangle and is not a render path. */
@@ -252,7 +257,7 @@ int mcpt_write_pfm(const char* path, const float* rgb, int width, int height);
 /* ---- tuning / A-B knobs ---------------------------------------------------------------------- */
 /* The library never reads the caller's environment.  Knobs (clamped to their valid range): "shade_threshold",
  * "cam_threshold" [1,32], "tri_cap" [1,64], "chunks" [0,64; 0 = automatic], "sah_ci", "sah_eb" [0.05,100] (next
- * tree build), "leaf_bfs", "sah_resort", "build_timing", "sm_stats", "verify_layout" {0,1}, "min_blocks" {0 = automatic, 4, 5, 6, 8}, "pool" {0, 1: the experimental pooled-lane kernel, csrc/render_pool.cuh}, "variant" (MCPT_TUNE builds);
+ * tree build), "leaf_bfs", "sah_resort", "build_timing", "sm_stats", "verify_layout", "device_pack" {0,1}, "min_blocks" {0 = automatic, 4, 5, 6, 8}, "pool" {0, 1: the experimental pooled-lane kernel, csrc/render_pool.cuh}, "variant" (MCPT_TUNE builds);
  * "defaults" restores the shipped configuration.  None of them changes a result beyond fp32 summation order. */
 int mcpt_set_tuning(const char* name, double value);
 int mcpt_get_tuning(const char* name, double* value);

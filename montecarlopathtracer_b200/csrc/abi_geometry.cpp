@@ -57,6 +57,39 @@ void release_device_scene(Context& c) {
 // failed call leaves the previous geometry (host tables, tree AND device tables) exactly as it was.  If the upload
 // of a committed scene fails, the context holds the new host tables with nothing on the device (uploaded = false;
 // the next device call retries the upload) -- never a mix of new host tables and old device tables.
+// The small tables (materials, emitters) go up, the scene descriptor is bound to the device tables, residency is chosen.
+int bind_device_scene(Context& c) {
+    cudaError_t e;
+    if ((e = upload(c.d_mats, c.packed.mats, c.stream)) != cudaSuccess) return fail_cuda(e, "upload mats");
+    if ((e = upload(c.d_emitters, c.packed.emitters, c.stream)) != cudaSuccess) return fail_cuda(e, "upload emitters");
+    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "scene upload");
+    c.parity_uploaded = false;
+    c.dscene = DScene{};
+    DScene& d = c.dscene;
+    d.rope_nodes = c.d_rope_nodes.ptr; d.leaf_blob = c.d_leaf_blob.ptr; d.tri_shade = c.d_tri_shade.ptr; d.mats = c.d_mats.ptr; d.emitters = c.d_emitters.ptr;
+    for (int i = 0; i < 3; ++i) { d.bmin[i] = c.packed.bmin[i]; d.bmax[i] = c.packed.bmax[i]; }
+    d.num_nodes = static_cast<uint32_t>(c.tree.num_nodes());
+    d.num_tris = static_cast<uint32_t>(c.scene.num_triangles());
+    d.num_mats = static_cast<uint32_t>(c.scene.num_materials());
+    d.num_emitters = c.packed.emitter_area > 0 ? static_cast<uint32_t>(c.packed.emitters.size() / 3) : 0u;
+    d.emitter_area = c.packed.emitter_area;
+    // Scenes whose render-path tables do not fit L2 are latency-bound: they render with 8 resident blocks per SM
+    // (launch.cu).  A persisting-L2 window over rope_nodes was measured there too: no effect (profiles/r2_tuning.md).
+    int l2 = 0;
+    cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, c.device);
+    c.render_path_bytes = c.tree.num_nodes() * sizeof(uint2) + (c.blob_float4s + 3 * c.scene.num_triangles()) * sizeof(float4);
+    c.large_scene = l2 > 0 && c.render_path_bytes > static_cast<size_t>(l2);
+    c.uploaded = true;
+    return MCPT_OK;
+}
+
+// Builds tree and device tables into locals and commits them to the context only when all of it succeeded: a
+// failed call leaves the previous geometry (host tables, tree) exactly as it was.  If the upload
+// of a committed scene fails, the context holds the new host tables with nothing on the device (uploaded = false;
+// the next device call retries the upload) -- never a mix of new host tables and old device tables.
+// MCPT_BUILD_GPU with the device pack writes the new render-path tables straight into the context's device buffers: the
+// previous scene's device tables are given up first (uploaded = false), and come back from its host tables on the next device
+// call should the build fail.
 int install_scene(HostScene&& scene, int build_mode) {
     Context& c = ctx();
     std::string err;
@@ -64,30 +97,54 @@ int install_scene(HostScene&& scene, int build_mode) {
     if (!validate_scene(scene, err)) return fail(MCPT_ERR_INVALID, err);
     HostTree tree;
     PackedScene packed;
+    DeviceTables dt;
+    bool devicePacked = false;
     const auto tStart = std::chrono::steady_clock::now();
     if (build_mode == MCPT_BUILD_GPU) {
         if (const int rc = bind_device()) return rc;   // the device builder has no host twin to fall back on: MCPT_BUILD_SAH is the host one
-        if (!build_gpu_tree(scene, tree, err)) return fail(MCPT_ERR_CUDA, err);
+        const bool wantPack = tuning().device_pack != 0 && !tuning().leaf_bfs;
+        if (wantPack) {
+            dt.leaf_blob = &c.d_leaf_blob; dt.rope_nodes = &c.d_rope_nodes; dt.tri_shade = &c.d_tri_shade;
+            c.uploaded = false; c.parity_uploaded = false;
+        }
+        if (!build_gpu_tree(scene, tree, err, wantPack ? &dt : nullptr)) return fail(err.rfind("scene too large", 0) == 0 ? MCPT_ERR_INVALID : MCPT_ERR_CUDA, err);
+        devicePacked = wantPack && dt.done;
     } else {
         build_kd_tree(scene, build_mode, tree);
     }
     const auto tTree = std::chrono::steady_clock::now();
-    if (!pack_scene(scene, tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
+    if (devicePacked) {
+        pack_small_tables(scene, tree, packed);
+    } else {
+        if (!pack_scene(scene, tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
+        if (tuning().verify_layout && !check_ropes(tree, packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
+    }
     const auto tPack = std::chrono::steady_clock::now();
-    if (tuning().verify_layout && !check_ropes(tree, packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
     c.scene = std::move(scene);
     c.tree = std::move(tree);
     c.packed = std::move(packed);
+    c.host_packed = !devicePacked;
     c.has_geometry = true;
     c.uploaded = false;
     int rc = MCPT_OK;
-    if (c.has_device) {
+    if (devicePacked) {
+        c.blob_float4s = dt.blob_float4s;
+        rc = bind_device_scene(c);
+        if (rc == MCPT_OK && tuning().verify_layout) {   // the host's own pack of the same tree, checked and compared with what the device made
+            uint64_t bad[3];
+            if ((rc = ensure_host_packed()) == MCPT_OK && !check_ropes(c.tree, c.packed, err)) rc = fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
+            if (rc == MCPT_OK && (rc = compare_device_tables(bad)) == MCPT_OK && (bad[0] | bad[1] | bad[2]))
+                rc = fail(MCPT_ERR_INTERNAL, "device pack differs from the host pack");
+        }
+        if (rc != MCPT_OK) { cudaSetDevice(c.device); release_device_scene(c); }
+    } else if (c.has_device) {
         rc = ensure_uploaded();
         if (rc != MCPT_OK) { cudaSetDevice(c.device); release_device_scene(c); }
     }
     if (tuning().build_timing) {
         auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return 1e3 * std::chrono::duration<double>(b - a).count(); };
-        std::fprintf(stderr, "install: tree %.1f ms, pack + neighbour links %.1f ms, upload %.1f ms\n", ms(tStart, tTree), ms(tTree, tPack), ms(tPack, std::chrono::steady_clock::now()));
+        std::fprintf(stderr, "install: tree%s %.1f ms, %s %.1f ms, upload %.1f ms\n", devicePacked ? " + device pack" : "", ms(tStart, tTree),
+                     devicePacked ? "small tables" : "pack + neighbour links", ms(tTree, tPack), ms(tPack, std::chrono::steady_clock::now()));
     }
     return rc;
 }
@@ -102,6 +159,7 @@ int ensure_parity_uploaded() {
     Context& c = ctx();
     if (const int rc = ensure_uploaded()) return rc;
     if (c.parity_uploaded) return MCPT_OK;
+    if (const int rc = ensure_host_packed()) return rc;
     pack_parity_tables(c.tree, c.packed);
     cudaError_t e;
     if ((e = upload(c.d_ref_nodes, c.packed.ref_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload ref_nodes");
@@ -116,37 +174,51 @@ int ensure_parity_uploaded() {
     return MCPT_OK;
 }
 
+int ensure_host_packed() {
+    Context& c = ctx();
+    if (c.host_packed) return MCPT_OK;
+    if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry: call mcpt_create_geometry / mcpt_load_obj first");
+    PackedScene packed;
+    if (!pack_scene(c.scene, c.tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
+    c.packed = std::move(packed);
+    c.host_packed = true;
+    return MCPT_OK;
+}
+
 int ensure_uploaded() {
     Context& c = ctx();
     if (const int rc = bind_device()) return rc;
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry: call mcpt_create_geometry / mcpt_load_obj first");
     if (c.uploaded) return MCPT_OK;
+    if (const int rc = ensure_host_packed()) return rc;
     cudaError_t e;
-    c.parity_uploaded = false;
-    c.dscene = DScene{};
     if ((e = upload(c.d_leaf_blob, c.packed.leaf_blob, c.stream)) != cudaSuccess) return fail_cuda(e, "upload leaf_blob");
     if ((e = upload(c.d_rope_nodes, c.packed.rope_nodes, c.stream)) != cudaSuccess) return fail_cuda(e, "upload rope_nodes");
     if ((e = upload(c.d_tri_shade, c.packed.tri_shade, c.stream)) != cudaSuccess) return fail_cuda(e, "upload tri_shade");
-    if ((e = upload(c.d_mats, c.packed.mats, c.stream)) != cudaSuccess) return fail_cuda(e, "upload mats");
-    if ((e = upload(c.d_emitters, c.packed.emitters, c.stream)) != cudaSuccess) return fail_cuda(e, "upload emitters");
-    if ((e = cudaStreamSynchronize(c.stream)) != cudaSuccess) return fail_cuda(e, "scene upload");
-    DScene& d = c.dscene;
-    d.rope_nodes = c.d_rope_nodes.ptr; d.leaf_blob = c.d_leaf_blob.ptr; d.tri_shade = c.d_tri_shade.ptr; d.mats = c.d_mats.ptr; d.emitters = c.d_emitters.ptr;
-    for (int i = 0; i < 3; ++i) { d.bmin[i] = c.packed.bmin[i]; d.bmax[i] = c.packed.bmax[i]; }
-    d.num_nodes = static_cast<uint32_t>(c.tree.num_nodes());
-    d.num_tris = static_cast<uint32_t>(c.scene.num_triangles());
-    d.num_mats = static_cast<uint32_t>(c.scene.num_materials());
-    d.num_emitters = c.packed.emitter_area > 0 ? static_cast<uint32_t>(c.packed.emitters.size() / 3) : 0u;
-    d.emitter_area = c.packed.emitter_area;
-    // Scenes whose render-path tables do not fit L2 are latency-bound: they render with 8 resident blocks per SM
-    // (launch.cu).  A persisting-L2 window over rope_nodes was measured there too: no effect (profiles/r2_tuning.md).
-    {
-        int l2 = 0;
-        cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, c.device);
-        const size_t renderPath = c.packed.rope_nodes.size() * sizeof(uint2) + (c.packed.leaf_blob.size() + c.packed.tri_shade.size()) * sizeof(float4);
-        c.large_scene = l2 > 0 && renderPath > static_cast<size_t>(l2);
-    }
-    c.uploaded = true;
+    c.blob_float4s = c.packed.leaf_blob.size();
+    return bind_device_scene(c);
+}
+
+// Diagnostic: the device's render-path tables against the host's own pack of the same tree, word for word.
+// bad = {leaf_blob float4s, rope_nodes, tri_shade float4s} that differ.
+int compare_device_tables(uint64_t bad[3]) {
+    Context& c = ctx();
+    bad[0] = bad[1] = bad[2] = 0;
+    if (const int rc = ensure_uploaded()) return rc;
+    if (const int rc = ensure_host_packed()) return rc;
+    if (c.blob_float4s != c.packed.leaf_blob.size()) return fail(MCPT_ERR_INTERNAL, "leaf_blob size differs between the device and the host pack");
+    auto diff = [&](const void* dev, const void* host, size_t bytes, size_t unit, uint64_t& out) -> int {
+        std::vector<unsigned char> tmp(bytes);
+        const cudaError_t e = cudaMemcpy(tmp.data(), dev, bytes, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) return fail_cuda(e, "table download");
+        const unsigned char* h = static_cast<const unsigned char*>(host);
+        for (size_t i = 0; i < bytes; i += unit) out += std::memcmp(tmp.data() + i, h + i, unit) != 0 ? 1u : 0u;
+        return MCPT_OK;
+    };
+    int rc;
+    if ((rc = diff(c.d_leaf_blob.ptr, c.packed.leaf_blob.data(), c.packed.leaf_blob.size() * 16, 16, bad[0]))) return rc;
+    if ((rc = diff(c.d_rope_nodes.ptr, c.packed.rope_nodes.data(), c.packed.rope_nodes.size() * 8, 8, bad[1]))) return rc;
+    if ((rc = diff(c.d_tri_shade.ptr, c.packed.tri_shade.data(), c.packed.tri_shade.size() * 16, 16, bad[2]))) return rc;
     return MCPT_OK;
 }
 
@@ -199,7 +271,7 @@ int mcpt_shutdown(void) {
     }
     c.has_device = false;
     c.device = -1;
-    c.has_geometry = false;
+    c.has_geometry = false; c.host_packed = false;
     c.scene = HostScene(); c.tree = HostTree(); c.packed = PackedScene();
     return MCPT_OK;
     });
@@ -250,7 +322,7 @@ int mcpt_destroy_geometry(void) {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (c.has_device) { cudaSetDevice(c.device); release_device_scene(c); }
-    c.has_geometry = false;
+    c.has_geometry = false; c.host_packed = false;
     c.scene = HostScene(); c.tree = HostTree(); c.packed = PackedScene();
     return MCPT_OK;
     });
@@ -261,9 +333,19 @@ int mcpt_check_stackless_layout(void) {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
+    if (const int rc = ensure_host_packed()) return rc;
     std::string err;
     if (!check_ropes(c.tree, c.packed, err)) return fail(MCPT_ERR_INTERNAL, "stackless layout: " + err);
     return MCPT_OK;
+    });
+}
+
+int mcpt_debug_compare_device_tables(uint64_t differing[3]) {
+    return guarded([&]() -> int {
+    Context& c = ctx();
+    std::lock_guard<std::mutex> g(c.lock);
+    if (!differing) return fail(MCPT_ERR_INVALID, "null result");
+    return compare_device_tables(differing);
     });
 }
 
@@ -274,6 +356,7 @@ int mcpt_debug_stackless_walk(const float* ray6, int max_hops, int* hops, uint32
     std::lock_guard<std::mutex> g(c.lock);
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
     if (!ray6 || !hops || !leaf_offsets || !exit_t || !exit_axis || max_hops <= 0) return fail(MCPT_ERR_INVALID, "bad arguments");
+    if (const int rc = ensure_host_packed()) return rc;
     *hops = walk_ropes_host(c.packed, ray6, max_hops, leaf_offsets, exit_t, exit_axis);
     int n = 0;
     if (tri_ids && num_ids) {   // triangle ids of the visited leaves, -1 between leaves
@@ -306,7 +389,11 @@ int mcpt_get_tree_info(mcpt_tree_info* info) {
     info->max_depth = static_cast<int32_t>(c.tree.max_depth);
     info->num_emitter_triangles = c.packed.emitter_area > 0 ? static_cast<int32_t>(c.packed.emitters.size() / 3) : 0;
     info->build_seconds = c.tree.build_seconds;
-    info->device_bytes = c.packed.bytes();
+    // what is resident for rendering (+ the parity-only tables once something asked for them); before the first upload: the host pack's size
+    info->device_bytes = c.uploaded ? c.render_path_bytes + (c.packed.mats.size() + c.packed.emitters.size()) * sizeof(float4) +
+                                          (c.parity_uploaded ? c.packed.ref_nodes.size() * 16 + c.packed.kd_nodes.size() * 8 + c.packed.leaf_ids.size() * 4 +
+                                                                   (c.packed.tri_isect.size() + c.packed.leaf_tris.size()) * 16 : 0)
+                                    : c.packed.bytes();
     return MCPT_OK;
     });
 }
@@ -371,6 +458,7 @@ int mcpt_set_tuning(const char* name, double value) {
     else if (k == "build_timing") t.build_timing = clampi(0, 1);
     else if (k == "sm_stats") t.sm_stats = clampi(0, 1);
     else if (k == "verify_layout") t.verify_layout = clampi(0, 1);
+    else if (k == "device_pack") t.device_pack = clampi(0, 1);
     else if (k == "sah_ci") t.sah_ci = clampf(0.05f, 100.0f);
     else if (k == "sah_eb") t.sah_eb = clampf(0.05f, 100.0f);
     else if (k == "defaults") t = Tuning();
@@ -398,6 +486,7 @@ int mcpt_get_tuning(const char* name, double* value) {
     else if (k == "build_timing") *value = t.build_timing;
     else if (k == "sm_stats") *value = t.sm_stats;
     else if (k == "verify_layout") *value = t.verify_layout;
+    else if (k == "device_pack") *value = t.device_pack;
     else if (k == "sah_ci") *value = t.sah_ci;
     else if (k == "sah_eb") *value = t.sah_eb;
     else return fail(MCPT_ERR_INVALID, "unknown tuning knob: " + k);

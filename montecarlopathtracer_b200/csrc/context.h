@@ -32,6 +32,15 @@ struct DeviceBuffer {
     }
 };
 
+// kd_build_gpu.cu's device pack writes the render-path tables straight into these buffers of the context.
+struct DeviceTables {
+    DeviceBuffer<float4>* leaf_blob = nullptr;
+    DeviceBuffer<uint2>* rope_nodes = nullptr;
+    DeviceBuffer<float4>* tri_shade = nullptr;
+    size_t blob_float4s = 0;   // out: float4 units of leaf_blob in use (blocks + 3 of padding)
+    bool done = false;         // out: the three tables are complete on the device
+};
+
 struct Context {
     std::mutex lock;
     bool has_device = false;
@@ -40,10 +49,12 @@ struct Context {
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
 
     bool has_geometry = false, uploaded = false, parity_uploaded = false;   // render-path tables / parity-hook tables in HBM
+    bool host_packed = false;     // `packed` holds the host copy of the tables (not after a device pack, until something asks for it)
     HostScene scene;
     HostTree tree;
     PackedScene packed;
     DScene dscene{};
+    size_t blob_float4s = 0, render_path_bytes = 0;   // leaf_blob in use on the device; bytes of the tables a render reads
     bool large_scene = false;     // render-path tables larger than L2: latency-bound, rendered with 8 resident blocks per SM
     DeviceBuffer<float4> d_ref_nodes, d_tri_isect, d_leaf_tris, d_leaf_blob, d_tri_shade, d_mats, d_emitters;
     DeviceBuffer<uint2> d_kd_nodes, d_rope_nodes;
@@ -66,6 +77,8 @@ struct Context {
 Context& ctx();
 int fail(int code, const std::string& msg);
 int fail_cuda(cudaError_t e, const char* what);
+int compare_device_tables(uint64_t bad[3]);   // device render-path tables against the host pack of the same tree (diagnostic)
+int ensure_host_packed();   // the host copy of the packed tables (pack_scene on c.scene / c.tree) if a device pack skipped it
 int ensure_uploaded();  // needs lock held; binds the context's device to the calling thread; render-path tables
 int ensure_parity_uploaded();  // + the tables only the parity hooks and the A/B kernels read (first use)
 int bind_device();      // cudaSetDevice(context device): the current device is per host thread, so every entry point

@@ -16,8 +16,61 @@ inline float as_float(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
 inline uint32_t as_uint(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
 }  // namespace
 
+// Emitter list (triangle order, area CDF) and material table: the two small tables, shared by the host pack and by the device
+// pack (kd_build_gpu.cu makes the large ones on the device; these stay a host loop over the triangles' materials).
+static void collect_emitters(const HostScene& scene, PackedScene& out, std::vector<double>& areas, double& areaSum) {
+    const size_t nT = scene.num_triangles();
+    out.emitters.clear();
+    areas.clear();
+    areaSum = 0.0;
+    for (size_t t = 0; t < nT; ++t) {  // emitters keep triangle order: sequential
+        const uint32_t* r = &scene.triangles[7 * t];
+        // Emitter iff any Ka component > 0 (rtx.hlsl:330).
+        const float* Ka = &scene.materials[12 * static_cast<size_t>(r[6])];
+        if (!(Ka[0] > 0 || Ka[1] > 0 || Ka[2] > 0)) continue;
+        const float* a = &scene.vertices[3 * static_cast<size_t>(r[0])];
+        const float* b = &scene.vertices[3 * static_cast<size_t>(r[1])];
+        const float* c = &scene.vertices[3 * static_cast<size_t>(r[2])];
+        const double u[3] = {double(b[0]) - a[0], double(b[1]) - a[1], double(b[2]) - a[2]};
+        const double v[3] = {double(c[0]) - a[0], double(c[1]) - a[1], double(c[2]) - a[2]};
+        const double cx = u[1] * v[2] - u[2] * v[1], cy = u[2] * v[0] - u[0] * v[2], cz = u[0] * v[1] - u[1] * v[0];
+        const double area = 0.5 * std::sqrt(cx * cx + cy * cy + cz * cz);
+        areas.push_back(area);
+        areaSum += area;
+        out.emitters.push_back(make_float4(a[0], a[1], a[2], static_cast<float>(area)));
+        out.emitters.push_back(make_float4(static_cast<float>(u[0]), static_cast<float>(u[1]), static_cast<float>(u[2]), 0.0f));
+        out.emitters.push_back(make_float4(static_cast<float>(v[0]), static_cast<float>(v[1]), static_cast<float>(v[2]), as_float(static_cast<uint32_t>(t))));
+    }
+}
+static void pack_small_tables_finish(const HostScene& scene, PackedScene& out, const std::vector<double>& areas, double areaSum) {
+    const size_t nM = scene.num_materials();
+    // running CDF over emitter area for area-uniform light sampling
+    double run = 0.0;
+    for (size_t i = 0; i < areas.size(); ++i) {
+        run += areas[i];
+        out.emitters[3 * i + 1].w = (i + 1 == areas.size()) ? 1.0f : static_cast<float>(run / areaSum);
+    }
+    out.emitter_area = static_cast<float>(areaSum);
+    if (out.emitters.empty()) out.emitters.resize(3, make_float4(0, 0, 0, 0));
+
+    out.mats.resize(3 * nM);
+    for (size_t m = 0; m < nM; ++m) {
+        const float* p = &scene.materials[12 * m];
+        out.mats[3 * m] = make_float4(p[0], p[1], p[2], p[9]);       // Ka, Ns
+        out.mats[3 * m + 1] = make_float4(p[3], p[4], p[5], p[10]);  // Kd, Tr
+        out.mats[3 * m + 2] = make_float4(p[6], p[7], p[8], p[11]);  // Ks, Ni
+    }
+}
+void pack_small_tables(const HostScene& scene, const HostTree& tree, PackedScene& out) {
+    std::vector<double> areas;
+    double areaSum = 0.0;
+    collect_emitters(scene, out, areas, areaSum);
+    pack_small_tables_finish(scene, out, areas, areaSum);
+    for (int i = 0; i < 3; ++i) { out.bmin[i] = tree.aabb[i]; out.bmax[i] = tree.aabb[3 + i]; }
+}
+
 bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) {
-    const size_t nN = tree.num_nodes(), nT = scene.num_triangles(), nM = scene.num_materials();
+    const size_t nN = tree.num_nodes(), nT = scene.num_triangles();
     auto tp = std::chrono::steady_clock::now();
     auto lap = [&](const char* what) {
         if (!tuning().build_timing) return;
@@ -74,7 +127,6 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
     lap("node tables");
     out.tri_isect.resize(3 * nT);
     out.tri_shade.resize(3 * nT);
-    out.emitters.clear();
     double areaSum = 0.0;
     std::vector<double> areas;
 #pragma omp parallel for schedule(static) if (nT > 65536)
@@ -97,45 +149,12 @@ bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) 
         out.tri_shade[3 * t + 2] = make_float4(n2[0], n2[1], n2[2], 0.0f);
     }
     lap("triangle tables");
-    for (size_t t = 0; t < nT; ++t) {  // emitters keep triangle order: sequential
-        const uint32_t* r = &scene.triangles[7 * t];
-        const float* a = &scene.vertices[3 * static_cast<size_t>(r[0])];
-        const float* b = &scene.vertices[3 * static_cast<size_t>(r[1])];
-        const float* c = &scene.vertices[3 * static_cast<size_t>(r[2])];
-        // Emitter iff any Ka component > 0 (rtx.hlsl:330).
-        const float* Ka = &scene.materials[12 * static_cast<size_t>(r[6])];
-        if (Ka[0] > 0 || Ka[1] > 0 || Ka[2] > 0) {
-            const double u[3] = {double(b[0]) - a[0], double(b[1]) - a[1], double(b[2]) - a[2]};
-            const double v[3] = {double(c[0]) - a[0], double(c[1]) - a[1], double(c[2]) - a[2]};
-            const double cx = u[1] * v[2] - u[2] * v[1], cy = u[2] * v[0] - u[0] * v[2], cz = u[0] * v[1] - u[1] * v[0];
-            const double area = 0.5 * std::sqrt(cx * cx + cy * cy + cz * cz);
-            areas.push_back(area);
-            areaSum += area;
-            out.emitters.push_back(make_float4(a[0], a[1], a[2], static_cast<float>(area)));
-            out.emitters.push_back(make_float4(static_cast<float>(u[0]), static_cast<float>(u[1]), static_cast<float>(u[2]), 0.0f));
-            out.emitters.push_back(make_float4(static_cast<float>(v[0]), static_cast<float>(v[1]), static_cast<float>(v[2]), as_float(static_cast<uint32_t>(t))));
-        }
-    }
+    collect_emitters(scene, out, areas, areaSum);
     lap("emitters");
     const bool ropesOk = build_ropes(tree, out);
     lap("neighbour links + leaf blocks");
 
-    // running CDF over emitter area for area-uniform light sampling
-    double run = 0.0;
-    for (size_t i = 0; i < areas.size(); ++i) {
-        run += areas[i];
-        out.emitters[3 * i + 1].w = (i + 1 == areas.size()) ? 1.0f : static_cast<float>(run / areaSum);
-    }
-    out.emitter_area = static_cast<float>(areaSum);
-    if (out.emitters.empty()) out.emitters.resize(3, make_float4(0, 0, 0, 0));
-
-    out.mats.resize(3 * nM);
-    for (size_t m = 0; m < nM; ++m) {
-        const float* p = &scene.materials[12 * m];
-        out.mats[3 * m] = make_float4(p[0], p[1], p[2], p[9]);       // Ka, Ns
-        out.mats[3 * m + 1] = make_float4(p[3], p[4], p[5], p[10]);  // Kd, Tr
-        out.mats[3 * m + 2] = make_float4(p[6], p[7], p[8], p[11]);  // Ks, Ni
-    }
+    pack_small_tables_finish(scene, out, areas, areaSum);
     return ropesOk;
 }
 

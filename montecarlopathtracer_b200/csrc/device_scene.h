@@ -74,6 +74,7 @@ struct PackedScene {
 };
 
 bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out);  // false: scene too large for the leaf-block layout
+void pack_small_tables(const HostScene& scene, const HostTree& tree, PackedScene& out);   // mats, emitters, scene box only (the device pack makes the rest)
 void pack_parity_tables(const HostTree& tree, PackedScene& out);  // ref_nodes, leaf_tris: built on first use (parity hooks, A/B kernels)
 bool build_ropes(const HostTree& tree, PackedScene& out);  // kd_ropes.cpp; needs kd_nodes, leaf_ids, tri_isect of pack_scene; false: too many leaf references
 bool check_ropes(const HostTree& tree, const PackedScene& packed, std::string& err);  // kd_ropes.cpp: structural check of leaf_blob / rope_nodes

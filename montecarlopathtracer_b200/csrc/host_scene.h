@@ -51,6 +51,7 @@ struct Tuning {
     int sah_resort = 0;        // A/B: the re-sorting SAH builder on every level
     int build_timing = 0;      // print builder phase timings to stderr
     int sm_stats = 0;          // MCPT_TUNE builds, VAR bit 3: print per-warp round statistics
+    int device_pack = 1;       // MCPT_BUILD_GPU: render-path tables made on the device as well (0: downloaded tree packed on the host, uploaded)
     int verify_layout = 0;     // run check_ropes on every geometry install (the render kernel's walk relies on consistent tables)
     float sah_ci = 1.0f;       // SAH: cost of a triangle test relative to a node step              [0.05, 100]
     float sah_eb = 1.0f;       // SAH: multiplier when one child is empty                            [0.05, 100]
@@ -61,7 +62,10 @@ Tuning& tuning();
 // mode 0: node-for-node the tree of KDTree.hpp:58-287; mode 1: own SAH builder.
 void build_kd_tree(const HostScene& scene, int mode, HostTree& out);
 // kd_build_gpu.cu: level-synchronous SAH build on the bound CUDA device (MCPT_BUILD_GPU), result in the same host layout
-bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err);
+// With `pack` the render-path tables (leaf blocks + neighbour links, location nodes, shading records) are made on the device too,
+// straight into the caller's buffers (context.h: DeviceTables): nothing of them is computed on the host or uploaded.
+struct DeviceTables;
+bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err, DeviceTables* pack = nullptr);
 void release_gpu_builder_scratch();   // the builder's device scratch block is kept between builds; mcpt_shutdown frees it
 
 // scene_io.cpp

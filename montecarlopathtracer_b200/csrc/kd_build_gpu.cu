@@ -24,6 +24,7 @@
 
 #include <cub/device/device_scan.cuh>
 
+#include "context.h"
 #include "host_scene.h"
 
 namespace mcpt {
@@ -333,6 +334,129 @@ __global__ void sort_leaves_kernel(const uint32_t* __restrict__ gAxis, const uin
     }
 }
 
+// ---- device pack: the render-path tables (leaf blocks with neighbour links, location nodes, shading records) made where the
+// tree already is, instead of on the host after a download and before an upload.  Same tables bit for bit as
+// pack_scene + build_ropes (device_scene.cpp, kd_ropes.cpp) produce from the downloaded tree (tests compare them).
+constexpr uint32_t kNoRope = 0xFFFFFFFFu, kRopeLeafBit = 0x80000000u, kHandleOffsetMask = 0x0FFFFFFFu;
+
+// bottom-up, one level per launch: leaves and leaf references under every node
+__global__ void under_kernel(uint32_t base, uint32_t n, const uint32_t* __restrict__ gLeft, const uint32_t* __restrict__ gAxis,
+                             const uint32_t* __restrict__ gLeafCnt, uint32_t* __restrict__ lu, uint32_t* __restrict__ ru) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t g = base + i;
+    if (gAxis[g] == 0u) { lu[g] = 1u; ru[g] = gLeafCnt[g]; return; }
+    const uint32_t L = gLeft[g];
+    lu[g] = lu[L] + lu[L + 1u]; ru[g] = ru[L] + ru[L + 1u];
+}
+// top-down: depth-first ordinal of the first leaf under a node and the references in front of it
+__global__ void first_kernel(uint32_t base, uint32_t n, const uint32_t* __restrict__ gLeft, const uint32_t* __restrict__ gAxis,
+                             const uint32_t* __restrict__ lu, const uint32_t* __restrict__ ru, uint32_t* __restrict__ first, uint32_t* __restrict__ off) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t g = base + i;
+    if (gAxis[g] == 0u) return;
+    const uint32_t L = gLeft[g];
+    first[L] = first[g]; off[L] = off[g];
+    first[L + 1u] = first[g] + lu[L]; off[L + 1u] = off[g] + ru[L];
+}
+// leaf handles (block offset in float4 units | min(count, 7) << 28) and the location-node table
+__global__ void handle_kernel(uint32_t total, const uint32_t* __restrict__ gLeft, const uint32_t* __restrict__ gAxis, const float* __restrict__ gPlane,
+                              const uint32_t* __restrict__ gLeafCnt, const uint32_t* __restrict__ first, const uint32_t* __restrict__ off,
+                              uint32_t* __restrict__ handle, uint2* __restrict__ ropeNodes, uint32_t* __restrict__ overflow) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= total) return;
+    if (gAxis[g] != 0u) { ropeNodes[g] = make_uint2(__float_as_uint(gPlane[g]), (gLeft[g] << 2) | (gAxis[g] - 1u)); handle[g] = 0u; return; }
+    const unsigned long long units = 4ull * first[g] + 3ull * off[g];
+    if (units >= kHandleOffsetMask) atomicExch(overflow, 1u);
+    const uint32_t cnt = gLeafCnt[g];
+    const uint32_t h = static_cast<uint32_t>(units) | ((cnt < 7u ? cnt : 7u) << 28);
+    handle[g] = h;
+    ropeNodes[g] = make_uint2(h, (cnt << 2) | 3u);
+}
+// kd_ropes.cpp Builder::tighten
+__device__ __forceinline__ uint32_t tighten_rope(uint32_t r, int fa, bool maxSide, const float* lo, const float* hi, const uint32_t* __restrict__ gLeft,
+                                                 const uint32_t* __restrict__ gAxis, const float* __restrict__ gPlane) {
+    while (r != kNoRope && gAxis[r] != 0u) {
+        const int ra = static_cast<int>(gAxis[r]) - 1;
+        const float s = gPlane[r];
+        const uint32_t left = gLeft[r];
+        if (ra == fa) r = maxSide ? left : left + 1u;
+        else if (s >= hi[ra]) r = left;
+        else if (s <= lo[ra]) r = left + 1u;
+        else break;
+    }
+    return r;
+}
+// top-down, one level per launch: a node hands each child its six neighbour links, pushed down to the deepest covering node
+__global__ void rope_level_kernel(uint32_t base, uint32_t n, const uint32_t* __restrict__ gLeft, const uint32_t* __restrict__ gAxis,
+                                  const float* __restrict__ gPlane, const float* __restrict__ gBox, uint32_t* __restrict__ ropes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t g = base + i;
+    if (gAxis[g] == 0u) return;
+    const int a = static_cast<int>(gAxis[g]) - 1;
+    const uint32_t L = gLeft[g], R = L + 1u;
+    uint32_t rl[6], rr[6];
+    for (int f = 0; f < 6; ++f) { rl[f] = ropes[6 * static_cast<size_t>(g) + f]; rr[f] = rl[f]; }
+    rl[2 * a + 1] = R;
+    rr[2 * a] = L;
+    float llo[3], lhi[3], rlo[3], rhi[3];
+    for (int k = 0; k < 3; ++k) {
+        llo[k] = gBox[6 * static_cast<size_t>(L) + k]; lhi[k] = gBox[6 * static_cast<size_t>(L) + 3 + k];
+        rlo[k] = gBox[6 * static_cast<size_t>(R) + k]; rhi[k] = gBox[6 * static_cast<size_t>(R) + 3 + k];
+    }
+    for (int f = 0; f < 6; ++f) {
+        ropes[6 * static_cast<size_t>(L) + f] = tighten_rope(rl[f], f >> 1, (f & 1) != 0, llo, lhi, gLeft, gAxis, gPlane);
+        ropes[6 * static_cast<size_t>(R) + f] = tighten_rope(rr[f], f >> 1, (f & 1) != 0, rlo, rhi, gLeft, gAxis, gPlane);
+    }
+}
+// one thread per leaf: header {cell.lo, first} {cell.hi, count} {links} + the triangle records of its id list
+// (device_scene.cpp's tri_isect record: {a, c3} {a - b, id} {a - c, 0}, every operation rounded on its own like the host's)
+__global__ void blob_kernel(uint32_t total, const uint32_t* __restrict__ gAxis, const float* __restrict__ gBox, const uint32_t* __restrict__ gLeafOff,
+                            const uint32_t* __restrict__ gLeafCnt, const uint32_t* __restrict__ leafIds, const uint32_t* __restrict__ off,
+                            const uint32_t* __restrict__ handle, const uint32_t* __restrict__ ropes, const float* __restrict__ verts,
+                            const uint32_t* __restrict__ tris, float4* __restrict__ blob) {
+    const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= total || gAxis[g] != 0u) return;
+    float4* blk = blob + (handle[g] & kHandleOffsetMask);
+    const uint32_t cnt = gLeafCnt[g];
+    const float* b = gBox + 6 * static_cast<size_t>(g);
+    blk[0] = make_float4(b[0], b[1], b[2], __uint_as_float(off[g]));
+    blk[1] = make_float4(b[3], b[4], b[5], __uint_as_float(cnt));
+    uint32_t enc[6];
+    for (int f = 0; f < 6; ++f) {
+        const uint32_t r = ropes[6 * static_cast<size_t>(g) + f];
+        enc[f] = (r != kNoRope && gAxis[r] == 0u) ? (kRopeLeafBit | handle[r]) : r;
+    }
+    blk[2] = make_float4(__uint_as_float(enc[0]), __uint_as_float(enc[1]), __uint_as_float(enc[2]), __uint_as_float(enc[3]));
+    blk[3] = make_float4(__uint_as_float(enc[4]), __uint_as_float(enc[5]), 0.0f, 0.0f);
+    for (uint32_t i = 0; i < cnt; ++i) {
+        const uint32_t t = leafIds[gLeafOff[g] + i];
+        const uint32_t* r = tris + 7 * static_cast<size_t>(t);
+        const float* va = verts + 3 * static_cast<size_t>(r[0]);
+        const float* vb = verts + 3 * static_cast<size_t>(r[1]);
+        const float* vc = verts + 3 * static_cast<size_t>(r[2]);
+        const float e1x = __fsub_rn(va[0], vb[0]), e1y = __fsub_rn(va[1], vb[1]), e1z = __fsub_rn(va[2], vb[2]);
+        const float e2x = __fsub_rn(va[0], vc[0]), e2y = __fsub_rn(va[1], vc[1]), e2z = __fsub_rn(va[2], vc[2]);
+        const float c3 = __fsub_rn(__fmul_rn(e1y, e2z), __fmul_rn(e2y, e1z));
+        blk[4 + 3 * i] = make_float4(va[0], va[1], va[2], c3);
+        blk[5 + 3 * i] = make_float4(e1x, e1y, e1z, __uint_as_float(t));
+        blk[6 + 3 * i] = make_float4(e2x, e2y, e2z, 0.0f);
+    }
+}
+__global__ void tri_shade_kernel(uint32_t nT, const float* __restrict__ normals, const uint32_t* __restrict__ tris, float4* __restrict__ out) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nT) return;
+    const uint32_t* r = tris + 7 * static_cast<size_t>(t);
+    const float* n0 = normals + 3 * static_cast<size_t>(r[3]);
+    const float* n1 = normals + 3 * static_cast<size_t>(r[4]);
+    const float* n2 = normals + 3 * static_cast<size_t>(r[5]);
+    out[3 * static_cast<size_t>(t)] = make_float4(n0[0], n0[1], n0[2], __uint_as_float(r[6]));
+    out[3 * static_cast<size_t>(t) + 1] = make_float4(n1[0], n1[1], n1[2], 0.0f);
+    out[3 * static_cast<size_t>(t) + 2] = make_float4(n2[0], n2[1], n2[2], 0.0f);
+}
+
 // Scratch comes from ONE grow-only device block kept between builds (cudaMalloc + cudaFree of the ~2 GB a 1 M-triangle build
 // touches cost 250 ms per call -- five times the levels themselves); mcpt_shutdown releases it (release_gpu_builder_scratch).
 struct Arena {
@@ -374,7 +498,7 @@ void release_gpu_builder_scratch() {
 namespace {
 // One attempt with room for `dup` references per triangle.  false + err: a CUDA error, or (tooSmall) the scene duplicates more
 // than that -- the caller retries with more room.
-bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err, size_t dup, bool& tooSmall) {
+bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err, size_t dup, bool& tooSmall, DeviceTables* pack) {
     const auto t0 = std::chrono::steady_clock::now();
     const uint32_t nT = static_cast<uint32_t>(scene.num_triangles());
     const size_t refCap = dup * nT + 4096, nodeCap = (dup + 2) * nT + 4096;
@@ -397,7 +521,8 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
         cub::DeviceScan::ExclusiveSum(nullptr, tmp, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(2 * levelCap + 1), s);
         const size_t need = scene.vertices.size() * 4 + scene.triangles.size() * 4 + 32ull * nT + 4 * refCap * 4 + 2 * (2 * levelCap) * sizeof(LevelNode) +
                             2 * levelCap * sizeof(Decision) + 12 * (2 * levelCap + 1) * 4 + (4 * levelCap + 2) * 4 + (refCap / kSmall + 2) * (3 * 2 * kBins * 4 + 8) +
-                            nodeCap * (4 * 4 + 24 + 4) + refCap * 4 + tmp + 256 + 64 * 256;
+                            nodeCap * (4 * 4 + 24 + 4) + refCap * 4 + tmp + 256 + 64 * 256 +
+                            (pack ? scene.normals.size() * 4 + nodeCap * (5 * 4 + 24) + 16 * 256 : 0);
         GK_CHECK(reserve_arena(need));
     }
     GK_CHECK(dVerts.alloc(scene.vertices.size())); GK_CHECK(dTris.alloc(scene.triangles.size()));
@@ -425,9 +550,11 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
     scene_box_kernel<<<1, 256, 0, s>>>(triLo.p, triHi.p, nT, level[0].p);
 
     uint32_t nNodes = 1, nRefs = nT, levelBase = 0, leafIdBase = 0, depthReached = 0;
+    std::vector<std::pair<uint32_t, uint32_t>> levels;   // (first node, node count) of every depth, for the device pack
     int cur = 0;
     for (int depth = 0; nNodes > 0; ++depth) {
         depthReached = static_cast<uint32_t>(depth);
+        levels.emplace_back(levelBase, nNodes);
         const int nxt = cur ^ 1;
         if (static_cast<size_t>(levelBase) + nNodes > nodeCap) { err = "GPU KD build: node capacity exceeded"; tooSmall = true; return false; }
         // scan sizes include one extra element so that the last entry of each exclusive sum is the level's total
@@ -486,6 +613,41 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
     sort_leaves_kernel<<<grid(total), B, 0, s>>>(gAxis.p, gLeafOff.p, gLeafCnt.p, total, leafIds.p);
     GK_CHECK(cudaGetLastError());
 
+    if (pack) {
+        // ---- device pack (kernels above): the tree never leaves the device on its way into the render-path tables ----
+        pack->done = false;
+        const size_t nodeCapUsed = total;
+        Dev<uint32_t> lu, ru, first, off, handle, ropes, overflow;
+        Dev<float> dNormals;
+        GK_CHECK(lu.alloc(nodeCapUsed)); GK_CHECK(ru.alloc(nodeCapUsed)); GK_CHECK(first.alloc(nodeCapUsed)); GK_CHECK(off.alloc(nodeCapUsed));
+        GK_CHECK(handle.alloc(nodeCapUsed)); GK_CHECK(ropes.alloc(6 * nodeCapUsed)); GK_CHECK(overflow.alloc(1));
+        GK_CHECK(dNormals.alloc(std::max<size_t>(scene.normals.size(), 1)));
+        if (!scene.normals.empty()) GK_CHECK(cudaMemcpyAsync(dNormals.p, scene.normals.data(), scene.normals.size() * 4, cudaMemcpyHostToDevice, s));
+        for (size_t d = levels.size(); d-- > 0;)
+            under_kernel<<<grid(levels[d].second), B, 0, s>>>(levels[d].first, levels[d].second, gLeft.p, gAxis.p, gLeafCnt.p, lu.p, ru.p);
+        GK_CHECK(cudaMemsetAsync(first.p, 0, 4, s)); GK_CHECK(cudaMemsetAsync(off.p, 0, 4, s)); GK_CHECK(cudaMemsetAsync(overflow.p, 0, 4, s));
+        GK_CHECK(cudaMemsetAsync(ropes.p, 0xFF, 6 * 4, s));   // the root has no neighbours
+        for (size_t d = 0; d < levels.size(); ++d) {
+            first_kernel<<<grid(levels[d].second), B, 0, s>>>(levels[d].first, levels[d].second, gLeft.p, gAxis.p, lu.p, ru.p, first.p, off.p);
+            rope_level_kernel<<<grid(levels[d].second), B, 0, s>>>(levels[d].first, levels[d].second, gLeft.p, gAxis.p, gPlane.p, gBox.p, ropes.p);
+        }
+        uint32_t counts[2] = {0, 0};
+        GK_CHECK(cudaMemcpyAsync(&counts[0], lu.p, 4, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(&counts[1], ru.p, 4, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaStreamSynchronize(s));
+        const size_t units = 4ull * counts[0] + 3ull * counts[1];
+        if (counts[1] != leafIdBase) { err = "GPU KD pack: reference count mismatch"; return false; }
+        if (units >= kHandleOffsetMask) { err = "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)"; return false; }
+        GK_CHECK(pack->leaf_blob->ensure(units + 3)); GK_CHECK(pack->rope_nodes->ensure(total)); GK_CHECK(pack->tri_shade->ensure(3ull * nT));
+        handle_kernel<<<grid(total), B, 0, s>>>(total, gLeft.p, gAxis.p, gPlane.p, gLeafCnt.p, first.p, off.p, handle.p, pack->rope_nodes->ptr, overflow.p);
+        blob_kernel<<<grid(total), B, 0, s>>>(total, gAxis.p, gBox.p, gLeafOff.p, gLeafCnt.p, leafIds.p, off.p, handle.p, ropes.p, dVerts.p, dTris.p, pack->leaf_blob->ptr);
+        GK_CHECK(cudaMemsetAsync(pack->leaf_blob->ptr + units, 0, 3 * sizeof(float4), s));   // a lane may read one record past a leaf of 7+ triangles' known count
+        tri_shade_kernel<<<grid(nT), B, 0, s>>>(nT, dNormals.p, dTris.p, pack->tri_shade->ptr);
+        GK_CHECK(cudaGetLastError());
+        pack->blob_float4s = units + 3;
+        pack->done = true;     // complete once the stream has drained (the synchronize below)
+    }
+
     out = HostTree();
     out.left.resize(total); out.aabb.resize(6 * static_cast<size_t>(total)); out.split_axis.resize(total); out.split_value.resize(total);
     out.leaf_offset.resize(total); out.leaf_count.resize(total); out.leaf_ids.resize(leafIdBase);
@@ -512,11 +674,11 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
 // Needs a bound CUDA device (the caller checks).  The scratch is sized for 6 references per triangle (tessellated surfaces
 // duplicate 1.3-2.5x); a scene that duplicates more -- a soup of large overlapping triangles -- is built again with room for
 // 16x, 40x, 100x.  false + err: beyond that, out of device memory, or a CUDA error.
-bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err) {
+bool build_gpu_tree(const HostScene& scene, HostTree& out, std::string& err, DeviceTables* pack) {
     const auto t0 = std::chrono::steady_clock::now();
     for (const size_t dup : {6u, 16u, 40u, 100u}) {
         bool tooSmall = false;
-        if (build_gpu_tree_with(scene, out, err, dup, tooSmall)) {
+        if (build_gpu_tree_with(scene, out, err, dup, tooSmall, pack)) {
             out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();   // retries included
             return true;
         }

@@ -82,6 +82,7 @@ def lib() -> C.CDLL:
     L.mcpt_get_tree_info.argtypes = [C.POINTER(TreeInfo)]
     L.mcpt_debug_stackless_walk.argtypes = [_vp, C.c_int, C.POINTER(C.c_int), _vp, _vp, _vp, _vp, C.c_int, C.POINTER(C.c_int)]
     L.mcpt_check_stackless_layout.argtypes = []
+    L.mcpt_debug_compare_device_tables.argtypes = [_vp]
     L.mcpt_get_tree.argtypes = [_vp] * 8
     L.mcpt_get_scene.argtypes = [_vp] * 5
     L.mcpt_default_render_cfg.argtypes = [C.POINTER(RenderCfg), C.c_int, C.c_int, C.c_int, C.c_int]
@@ -159,6 +160,13 @@ def load_scene_file(path: str, build_mode: int = BUILD_REFERENCE) -> None:
 
 def destroy_geometry() -> None:
     _check(lib().mcpt_destroy_geometry())
+
+
+def compare_device_tables() -> tuple[int, int, int]:
+    """(leaf-block float4s, nodes, shading float4s) in which the device's render-path tables differ from the host pack of the same tree."""
+    bad = (C.c_uint64 * 3)()
+    _check(lib().mcpt_debug_compare_device_tables(bad))
+    return int(bad[0]), int(bad[1]), int(bad[2])
 
 
 def check_stackless_layout() -> None:

@@ -129,3 +129,53 @@ def test_gpu_builder_at_one_million_triangles(gpu, oracle, scenes):
             assert (np.where(tri[bad] >= 0, t[bad], np.inf) > bt[bad]).all() and (edge < 4e-7).all()
     img = T.render_scene(T.render_cfg(256, 256, 16, 8, seed=2))
     assert np.isfinite(img).all() and img.mean() > 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["scene01", "scene02", "scene03"])
+def test_device_pack_equals_the_host_pack(gpu, scenes, name):
+    """MCPT_BUILD_GPU makes the render-path tables (leaf blocks with neighbour links, location nodes, shading records) on the
+    device; the host's pack_scene + build_ropes of the same downloaded tree must give the same words, and renders through
+    either must be the same image."""
+    T, s = gpu, scenes[name]
+    try:
+        T.set_tuning("defaults", 0)
+        T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_GPU)
+        assert T.compare_device_tables() == (0, 0, 0)
+        T.check_stackless_layout()
+        cfg = T.render_cfg(120, 90, 6, 5, seed=4)
+        a = T.render_scene(cfg); ra = T.counters().rays
+        rays = np.random.default_rng(3).normal(size=(4096, 6)).astype(np.float32); rays[:, :3] *= 3; rays[:, 1] += 5
+        hits_a = T.intersect_batch(rays, T.ISECT_ROPES)
+        T.set_tuning("device_pack", 0)
+        T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_GPU)
+        assert T.compare_device_tables() == (0, 0, 0)
+        b = T.render_scene(cfg); rb = T.counters().rays
+        hits_b = T.intersect_batch(rays, T.ISECT_ROPES)
+        assert np.array_equal(a, b) and ra == rb
+        for x, y in zip(hits_a, hits_b):
+            assert np.array_equal(x, y)
+    finally:
+        T.set_tuning("defaults", 0)
+
+
+@pytest.mark.gpu
+def test_device_pack_at_one_million_triangles(gpu, scenes):
+    from montecarlopathtracer_b200 import scenes as S
+    T = gpu
+    T.create_geometry(scenes["scene01_lambert"].verts, scenes["scene01_lambert"].normals, scenes["scene01_lambert"].tris, scenes["scene01_lambert"].mats, T.BUILD_SAH)
+    hf = S.cornell_heightfield(T.get_scene(), 708)
+    T.create_geometry(*hf, T.BUILD_GPU)
+    assert T.compare_device_tables() == (0, 0, 0)
+    T.check_stackless_layout()
+    # a refused scene after a device-packed one: the previous scene is untouched
+    img = T.render_scene(T.render_cfg(64, 48, 2, 5, seed=1))
+    bad = hf[2].copy(); bad[5, 1] = len(hf[0]) + 7      # a vertex index past the table
+    with pytest.raises(RuntimeError):
+        T.create_geometry(hf[0], hf[1], bad, hf[3], T.BUILD_GPU)
+    assert np.array_equal(T.render_scene(T.render_cfg(64, 48, 2, 5, seed=1)), img)
+    # the host copy of the tables appears when something asks for it (here: the parity tables of the stack traversal)
+    rays = np.random.default_rng(5).normal(size=(2048, 6)).astype(np.float32); rays[:, 1] += 5
+    a, b = T.intersect_batch(rays, T.ISECT_ROPES), T.intersect_batch(rays, T.ISECT_KD)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(_bits(a[1]), _bits(b[1]))
+    T.destroy_geometry()
