@@ -105,6 +105,7 @@ int install_scene(HostScene&& scene, int build_mode) {
         const bool wantPack = tuning().device_pack != 0 && !tuning().leaf_bfs;
         if (wantPack) {
             dt.leaf_blob = &c.d_leaf_blob; dt.rope_nodes = &c.d_rope_nodes; dt.tri_shade = &c.d_tri_shade;
+            dt.tree_words = &c.d_tree_words; dt.tree_floats = &c.d_tree_floats;   // the tree itself stays on the device until the host asks (ensure_host_tree)
             c.uploaded = false; c.parity_uploaded = false;
         }
         if (!build_gpu_tree(scene, tree, err, wantPack ? &dt : nullptr)) return fail(err.rfind("scene too large", 0) == 0 ? MCPT_ERR_INVALID : MCPT_ERR_CUDA, err);
@@ -126,6 +127,10 @@ int install_scene(HostScene&& scene, int build_mode) {
     c.host_packed = !devicePacked;
     c.has_geometry = true;
     c.uploaded = false;
+    if (c.tree.on_host && c.has_device && (c.d_tree_words.ptr || c.d_tree_floats.ptr)) {   // a previous device-built tree nobody asked for
+        cudaSetDevice(c.device);
+        c.d_tree_words.release(); c.d_tree_floats.release();
+    }
     int rc = MCPT_OK;
     if (devicePacked) {
         c.blob_float4s = dt.blob_float4s;
@@ -174,10 +179,38 @@ int ensure_parity_uploaded() {
     return MCPT_OK;
 }
 
+int ensure_host_tree() {
+    Context& c = ctx();
+    HostTree& t = c.tree;
+    if (t.on_host) return MCPT_OK;
+    if (const int rc = bind_device()) return rc;
+    const size_t n = t.nodes, r = t.refs;
+    if (c.d_tree_words.count < 4 * n + r || c.d_tree_floats.count < 7 * n || !c.d_tree_words.ptr || !c.d_tree_floats.ptr)
+        return fail(MCPT_ERR_INTERNAL, "the device-built tree is gone from the device before the host copied it");
+    t.left.resize(n); t.aabb.resize(6 * n); t.split_axis.resize(n); t.split_value.resize(n); t.leaf_offset.resize(n); t.leaf_count.resize(n); t.leaf_ids.resize(r);
+    const uint32_t* w = c.d_tree_words.ptr;
+    const float* f = c.d_tree_floats.ptr;
+    cudaError_t e = cudaMemcpy(t.left.data(), w, n * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(t.split_axis.data(), w + n, n * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(t.leaf_offset.data(), w + 2 * n, n * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(t.leaf_count.data(), w + 3 * n, n * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && r) e = cudaMemcpy(t.leaf_ids.data(), w + 4 * n, r * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(t.aabb.data(), f, n * 24, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess) e = cudaMemcpy(t.split_value.data(), f + 6 * n, n * 4, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+        t.left.clear(); t.aabb.clear(); t.split_axis.clear(); t.split_value.clear(); t.leaf_offset.clear(); t.leaf_count.clear(); t.leaf_ids.clear();
+        return fail_cuda(e, "tree download");
+    }
+    t.on_host = true;
+    c.d_tree_words.release(); c.d_tree_floats.release();
+    return MCPT_OK;
+}
+
 int ensure_host_packed() {
     Context& c = ctx();
     if (c.host_packed) return MCPT_OK;
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry: call mcpt_create_geometry / mcpt_load_obj first");
+    if (const int rc = ensure_host_tree()) return rc;
     PackedScene packed;
     if (!pack_scene(c.scene, c.tree, packed)) return fail(MCPT_ERR_INVALID, "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)");
     c.packed = std::move(packed);
@@ -261,6 +294,7 @@ int mcpt_shutdown(void) {
     if (c.has_device) {
         cudaSetDevice(c.device);
         release_device_scene(c);
+        c.d_tree_words.release(); c.d_tree_floats.release();
         release_gpu_builder_scratch();
         c.d_slices.release(); c.d_slices_sq.release(); c.d_sum.release(); c.d_sumsq.release(); c.d_rgb.release(); c.d_pool.release();
         c.d_frame_seeds.release(); c.d_counter.release(); c.d_rays.release(); c.d_t.release(); c.d_beta.release();
@@ -321,7 +355,7 @@ int mcpt_destroy_geometry(void) {
     return guarded([&]() -> int {
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
-    if (c.has_device) { cudaSetDevice(c.device); release_device_scene(c); }
+    if (c.has_device) { cudaSetDevice(c.device); release_device_scene(c); c.d_tree_words.release(); c.d_tree_floats.release(); }
     c.has_geometry = false; c.host_packed = false;
     c.scene = HostScene(); c.tree = HostTree(); c.packed = PackedScene();
     return MCPT_OK;
@@ -385,7 +419,7 @@ int mcpt_get_tree_info(mcpt_tree_info* info) {
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
     info->num_nodes = static_cast<int32_t>(c.tree.num_nodes());
     info->num_leaves = static_cast<int32_t>(c.tree.num_leaves);
-    info->num_leaf_refs = static_cast<int32_t>(c.tree.leaf_ids.size());
+    info->num_leaf_refs = static_cast<int32_t>(c.tree.num_refs());
     info->max_depth = static_cast<int32_t>(c.tree.max_depth);
     info->num_emitter_triangles = c.packed.emitter_area > 0 ? static_cast<int32_t>(c.packed.emitters.size() / 3) : 0;
     info->build_seconds = c.tree.build_seconds;
@@ -404,6 +438,7 @@ int mcpt_get_tree(uint32_t* left, uint32_t* right, float* aabb6, uint32_t* split
     Context& c = ctx();
     std::lock_guard<std::mutex> g(c.lock);
     if (!c.has_geometry) return fail(MCPT_ERR_INVALID, "no geometry");
+    if (const int rc = ensure_host_tree()) return rc;
     const HostTree& t = c.tree;
     const size_t n = t.num_nodes();
     if (left) std::memcpy(left, t.left.data(), n * 4);

@@ -37,6 +37,8 @@ struct DeviceTables {
     DeviceBuffer<float4>* leaf_blob = nullptr;
     DeviceBuffer<uint2>* rope_nodes = nullptr;
     DeviceBuffer<float4>* tri_shade = nullptr;
+    DeviceBuffer<uint32_t>* tree_words = nullptr;   // optional: the tree itself stays on the device too, [left | axis | leaf offset | leaf count] x nodes, then the leaf ids
+    DeviceBuffer<float>* tree_floats = nullptr;     //           [box 6 x nodes | plane x nodes]; the HostTree then carries counts only (on_host = false)
     size_t blob_float4s = 0;   // out: float4 units of leaf_blob in use (blocks + 3 of padding)
     bool done = false;         // out: the three tables are complete on the device
 };
@@ -58,7 +60,8 @@ struct Context {
     bool large_scene = false;     // render-path tables larger than L2: latency-bound, rendered with 8 resident blocks per SM
     DeviceBuffer<float4> d_ref_nodes, d_tri_isect, d_leaf_tris, d_leaf_blob, d_tri_shade, d_mats, d_emitters;
     DeviceBuffer<uint2> d_kd_nodes, d_rope_nodes;
-    DeviceBuffer<uint32_t> d_leaf_ids;
+    DeviceBuffer<uint32_t> d_leaf_ids, d_tree_words;   // d_tree_words / d_tree_floats: a device-built tree until the host asks for it
+    DeviceBuffer<float> d_tree_floats;
 
     // render scratch, grown on demand and kept
     DeviceBuffer<float4> d_slices, d_slices_sq, d_sum, d_sumsq;
@@ -78,6 +81,7 @@ Context& ctx();
 int fail(int code, const std::string& msg);
 int fail_cuda(cudaError_t e, const char* what);
 int compare_device_tables(uint64_t bad[3]);   // device render-path tables against the host pack of the same tree (diagnostic)
+int ensure_host_tree();     // downloads a device-built tree into c.tree if it is still on the device only
 int ensure_host_packed();   // the host copy of the packed tables (pack_scene on c.scene / c.tree) if a device pack skipped it
 int ensure_uploaded();  // needs lock held; binds the context's device to the calling thread; render-path tables
 int ensure_parity_uploaded();  // + the tables only the parity hooks and the A/B kernels read (first use)

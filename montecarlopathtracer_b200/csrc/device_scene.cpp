@@ -66,7 +66,7 @@ void pack_small_tables(const HostScene& scene, const HostTree& tree, PackedScene
     double areaSum = 0.0;
     collect_emitters(scene, out, areas, areaSum);
     pack_small_tables_finish(scene, out, areas, areaSum);
-    for (int i = 0; i < 3; ++i) { out.bmin[i] = tree.aabb[i]; out.bmax[i] = tree.aabb[3 + i]; }
+    for (int i = 0; i < 3; ++i) { out.bmin[i] = tree.root(i); out.bmax[i] = tree.root(3 + i); }
 }
 
 bool pack_scene(const HostScene& scene, const HostTree& tree, PackedScene& out) {

@@ -33,7 +33,14 @@ struct HostTree {
     uint32_t max_depth = 0;
     uint32_t num_leaves = 0;
     double build_seconds = 0.0;
-    size_t num_nodes() const { return left.size(); }
+    // A tree built AND packed on the device stays there until something on the host asks for it (context.h: ensure_host_tree):
+    // until then only the counts and the root box below are valid and the vectors above are empty.
+    bool on_host = true;
+    size_t nodes = 0, refs = 0;
+    float root_box[6] = {0, 0, 0, 0, 0, 0};
+    size_t num_nodes() const { return on_host ? left.size() : nodes; }
+    size_t num_refs() const { return on_host ? leaf_ids.size() : refs; }
+    float root(int i) const { return on_host ? aabb[static_cast<size_t>(i)] : root_box[i]; }
 };
 
 // Tuning and A/B knobs.  The library never reads the caller's environment: the only way to change them is

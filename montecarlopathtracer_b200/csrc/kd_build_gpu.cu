@@ -613,6 +613,7 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
     sort_leaves_kernel<<<grid(total), B, 0, s>>>(gAxis.p, gLeafOff.p, gLeafCnt.p, total, leafIds.p);
     GK_CHECK(cudaGetLastError());
 
+    uint32_t packLeaves = 0;
     if (pack) {
         // ---- device pack (kernels above): the tree never leaves the device on its way into the render-path tables ----
         pack->done = false;
@@ -636,6 +637,7 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
         GK_CHECK(cudaMemcpyAsync(&counts[1], ru.p, 4, cudaMemcpyDeviceToHost, s));
         GK_CHECK(cudaStreamSynchronize(s));
         const size_t units = 4ull * counts[0] + 3ull * counts[1];
+        packLeaves = counts[0];
         if (counts[1] != leafIdBase) { err = "GPU KD pack: reference count mismatch"; return false; }
         if (units >= kHandleOffsetMask) { err = "scene too large: more than 4 GiB of leaf blocks (28-bit leaf handles)"; return false; }
         GK_CHECK(pack->leaf_blob->ensure(units + 3)); GK_CHECK(pack->rope_nodes->ensure(total)); GK_CHECK(pack->tri_shade->ensure(3ull * nT));
@@ -649,17 +651,36 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
     }
 
     out = HostTree();
-    out.left.resize(total); out.aabb.resize(6 * static_cast<size_t>(total)); out.split_axis.resize(total); out.split_value.resize(total);
-    out.leaf_offset.resize(total); out.leaf_count.resize(total); out.leaf_ids.resize(leafIdBase);
-    GK_CHECK(cudaMemcpyAsync(out.left.data(), gLeft.p, total * 4ull, cudaMemcpyDeviceToHost, s));
-    GK_CHECK(cudaMemcpyAsync(out.aabb.data(), gBox.p, total * 24ull, cudaMemcpyDeviceToHost, s));
-    GK_CHECK(cudaMemcpyAsync(out.split_axis.data(), gAxis.p, total * 4ull, cudaMemcpyDeviceToHost, s));
-    GK_CHECK(cudaMemcpyAsync(out.split_value.data(), gPlane.p, total * 4ull, cudaMemcpyDeviceToHost, s));
-    GK_CHECK(cudaMemcpyAsync(out.leaf_offset.data(), gLeafOff.p, total * 4ull, cudaMemcpyDeviceToHost, s));
-    GK_CHECK(cudaMemcpyAsync(out.leaf_count.data(), gLeafCnt.p, total * 4ull, cudaMemcpyDeviceToHost, s));
-    if (leafIdBase) GK_CHECK(cudaMemcpyAsync(out.leaf_ids.data(), leafIds.p, leafIdBase * 4ull, cudaMemcpyDeviceToHost, s));
-    GK_CHECK(cudaStreamSynchronize(s));
-    for (uint32_t k = 0; k < total; ++k) out.num_leaves += out.split_axis[k] == 0 ? 1u : 0u;
+    if (pack && pack->done && pack->tree_words && pack->tree_floats) {
+        // the tree stays on the device (context buffers, so that it outlives the next build's scratch); the host gets the counts
+        const size_t n = total;
+        GK_CHECK(pack->tree_words->ensure(4 * n + leafIdBase)); GK_CHECK(pack->tree_floats->ensure(7 * n));
+        uint32_t* w = pack->tree_words->ptr;
+        float* f = pack->tree_floats->ptr;
+        GK_CHECK(cudaMemcpyAsync(w, gLeft.p, n * 4, cudaMemcpyDeviceToDevice, s));
+        GK_CHECK(cudaMemcpyAsync(w + n, gAxis.p, n * 4, cudaMemcpyDeviceToDevice, s));
+        GK_CHECK(cudaMemcpyAsync(w + 2 * n, gLeafOff.p, n * 4, cudaMemcpyDeviceToDevice, s));
+        GK_CHECK(cudaMemcpyAsync(w + 3 * n, gLeafCnt.p, n * 4, cudaMemcpyDeviceToDevice, s));
+        if (leafIdBase) GK_CHECK(cudaMemcpyAsync(w + 4 * n, leafIds.p, leafIdBase * 4ull, cudaMemcpyDeviceToDevice, s));
+        GK_CHECK(cudaMemcpyAsync(f, gBox.p, n * 24, cudaMemcpyDeviceToDevice, s));
+        GK_CHECK(cudaMemcpyAsync(f + 6 * n, gPlane.p, n * 4, cudaMemcpyDeviceToDevice, s));
+        GK_CHECK(cudaMemcpyAsync(out.root_box, gBox.p, 24, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaStreamSynchronize(s));
+        out.on_host = false; out.nodes = n; out.refs = leafIdBase;
+        out.num_leaves = packLeaves;
+    } else {
+        out.left.resize(total); out.aabb.resize(6 * static_cast<size_t>(total)); out.split_axis.resize(total); out.split_value.resize(total);
+        out.leaf_offset.resize(total); out.leaf_count.resize(total); out.leaf_ids.resize(leafIdBase);
+        GK_CHECK(cudaMemcpyAsync(out.left.data(), gLeft.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(out.aabb.data(), gBox.p, total * 24ull, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(out.split_axis.data(), gAxis.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(out.split_value.data(), gPlane.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(out.leaf_offset.data(), gLeafOff.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaMemcpyAsync(out.leaf_count.data(), gLeafCnt.p, total * 4ull, cudaMemcpyDeviceToHost, s));
+        if (leafIdBase) GK_CHECK(cudaMemcpyAsync(out.leaf_ids.data(), leafIds.p, leafIdBase * 4ull, cudaMemcpyDeviceToHost, s));
+        GK_CHECK(cudaStreamSynchronize(s));
+        for (uint32_t k = 0; k < total; ++k) out.num_leaves += out.split_axis[k] == 0 ? 1u : 0u;
+    }
     out.max_depth = depthReached;
     out.build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (tuning().build_timing) {
