@@ -67,10 +67,13 @@ __global__ void tri_bounds_kernel(const float* __restrict__ verts, const uint32_
 }
 
 // scene box = union of the triangle boxes (one block, enough for a one-off reduction over <= a few M triangles)
-__global__ void scene_box_kernel(const float4* __restrict__ triLo, const float4* __restrict__ triHi, uint32_t nT, LevelNode* root) {
+// Two stages: kBoxBlocks blocks reduce a slice each into partLo / partHi (root == nullptr), one block reduces those into the root node.
+constexpr unsigned kBoxBlocks = 256;
+__global__ void scene_box_kernel(const float4* __restrict__ triLo, const float4* __restrict__ triHi, uint32_t nT, LevelNode* root,
+                                 float4* __restrict__ partLo, float4* __restrict__ partHi, uint32_t rootRefs) {
     __shared__ float slo[3][256], shi[3][256];
     float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
-    for (uint32_t t = threadIdx.x; t < nT; t += 256) {
+    for (uint32_t t = blockIdx.x * 256u + threadIdx.x; t < nT; t += 256u * gridDim.x) {
         const float4 a = triLo[t], b = triHi[t];
         lo[0] = fminf(lo[0], a.x); lo[1] = fminf(lo[1], a.y); lo[2] = fminf(lo[2], a.z);
         hi[0] = fmaxf(hi[0], b.x); hi[1] = fmaxf(hi[1], b.y); hi[2] = fmaxf(hi[2], b.z);
@@ -86,8 +89,13 @@ __global__ void scene_box_kernel(const float4* __restrict__ triLo, const float4*
         __syncthreads();
     }
     if (threadIdx.x == 0) {
-        for (int i = 0; i < 3; ++i) { root->lo[i] = slo[i][0]; root->hi[i] = shi[i][0]; }
-        root->begin = 0; root->end = nT;
+        if (root) {
+            for (int i = 0; i < 3; ++i) { root->lo[i] = slo[i][0]; root->hi[i] = shi[i][0]; }
+            root->begin = 0; root->end = rootRefs;
+        } else {
+            partLo[blockIdx.x] = make_float4(slo[0][0], slo[1][0], slo[2][0], 0.f);
+            partHi[blockIdx.x] = make_float4(shi[0][0], shi[1][0], shi[2][0], 0.f);
+        }
     }
 }
 
@@ -186,6 +194,14 @@ __global__ void split_kernel(const LevelNode* __restrict__ nodes, uint32_t nNode
     out[k] = d;
 }
 
+// The references of a node are contiguous in the level's array, so the 32 lanes of a warp almost always work on ONE node: their
+// atomics on that node's counters are folded into one per warp (the top levels would otherwise send a million atomics to a
+// single address).  Returns true when every lane of the (full) warp is in range and names the same node.
+__device__ __forceinline__ bool warp_same_node(bool valid, uint32_t nd) {
+    const uint32_t lead = __shfl_sync(0xFFFFFFFFu, nd, 0);
+    return __all_sync(0xFFFFFFFFu, valid && nd == lead);
+}
+
 // Big nodes choose among equidistant planes; a plane through the middle of a row of triangles cuts (duplicates) all of them,
 // while the nearest reference bound next to it usually cuts none (exactly none on grid-aligned meshes such as K4's height
 // field).  snap_kernel finds, per big node, the reference bound nearest to the chosen plane (64-bit atomicMin on
@@ -194,21 +210,35 @@ __global__ void snap_kernel(const LevelNode* __restrict__ nodes, const Decision*
                             const uint32_t* __restrict__ refNode, uint32_t nRefs, const float4* __restrict__ triLo, const float4* __restrict__ triHi,
                             const uint32_t* __restrict__ binSlot, unsigned long long* __restrict__ snapKey) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nRefs) return;
-    const uint32_t nd = refNode[i];
-    const uint32_t slot = binSlot[nd];
-    if (slot == 0xFFFFFFFFu) return;
-    const Decision d = dec[nd];
-    if (d.axis < 0) return;
-    const LevelNode n = nodes[nd];
-    const float4 a = triLo[refTri[i]], b = triHi[refTri[i]];
-    const int ax = d.axis;
-    const float lo = fmaxf(ax == 0 ? a.x : (ax == 1 ? a.y : a.z), n.lo[ax]);
-    const float hi = fminf(ax == 0 ? b.x : (ax == 1 ? b.y : b.z), n.hi[ax]);
-    for (int side = 0; side < 2; ++side) {
-        const float c = (side ? hi : lo) + 0.0f;   // -0 -> +0
-        if (!(c > n.lo[ax] && c < n.hi[ax])) continue;   // strictly inside the cell: both children shrink
-        const unsigned long long key = (static_cast<unsigned long long>(__float_as_uint(fabsf(c - d.plane))) << 32) | __float_as_uint(c);
+    const bool valid = i < nRefs;
+    const uint32_t nd = valid ? refNode[i] : 0xFFFFFFFFu;
+    const bool uniform = warp_same_node(valid, nd);
+    unsigned long long key = ~0ull;
+    uint32_t slot = 0xFFFFFFFFu;
+    if (valid) {
+        slot = binSlot[nd];
+        const Decision d = dec[nd];
+        if (slot != 0xFFFFFFFFu && d.axis >= 0) {
+            const LevelNode n = nodes[nd];
+            const float4 a = triLo[refTri[i]], b = triHi[refTri[i]];
+            const int ax = d.axis;
+            const float lo = fmaxf(ax == 0 ? a.x : (ax == 1 ? a.y : a.z), n.lo[ax]);
+            const float hi = fminf(ax == 0 ? b.x : (ax == 1 ? b.y : b.z), n.hi[ax]);
+            for (int side = 0; side < 2; ++side) {
+                const float c = (side ? hi : lo) + 0.0f;   // -0 -> +0
+                if (!(c > n.lo[ax] && c < n.hi[ax])) continue;   // strictly inside the cell: both children shrink
+                const unsigned long long k2 = (static_cast<unsigned long long>(__float_as_uint(fabsf(c - d.plane))) << 32) | __float_as_uint(c);
+                key = k2 < key ? k2 : key;
+            }
+        }
+    }
+    if (uniform) {
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xFFFFFFFFu, key, o);
+            key = other < key ? other : key;
+        }
+        if ((threadIdx.x & 31u) == 0u && key != ~0ull && slot != 0xFFFFFFFFu) atomicMin(snapKey + slot, key);
+    } else if (key != ~0ull) {
         atomicMin(snapKey + slot, key);
     }
 }
@@ -238,13 +268,24 @@ __global__ void count_kernel(const LevelNode* __restrict__ nodes, const Decision
                              const uint32_t* __restrict__ refNode, uint32_t nRefs, const float4* __restrict__ triLo,
                              const float4* __restrict__ triHi, uint32_t* __restrict__ nL, uint32_t* __restrict__ nR) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nRefs) return;
-    const uint32_t nd = refNode[i];
-    const Decision d = dec[nd];
-    if (d.axis < 0) return;
-    const uint32_t c = classify(nodes[nd], d, triLo[refTri[i]], triHi[refTri[i]]);
-    if (c & 1u) atomicAdd(nL + nd, 1u);
-    if (c & 2u) atomicAdd(nR + nd, 1u);
+    const bool valid = i < nRefs;
+    const uint32_t nd = valid ? refNode[i] : 0xFFFFFFFFu;
+    const bool uniform = warp_same_node(valid, nd);
+    uint32_t c = 0u;
+    if (valid) {
+        const Decision d = dec[nd];
+        if (d.axis >= 0) c = classify(nodes[nd], d, triLo[refTri[i]], triHi[refTri[i]]);
+    }
+    if (uniform) {
+        const uint32_t l = __popc(__ballot_sync(0xFFFFFFFFu, (c & 1u) != 0u)), r = __popc(__ballot_sync(0xFFFFFFFFu, (c & 2u) != 0u));
+        if ((threadIdx.x & 31u) == 0u) {
+            if (l) atomicAdd(nL + nd, l);
+            if (r) atomicAdd(nR + nd, r);
+        }
+    } else {
+        if (c & 1u) atomicAdd(nL + nd, 1u);
+        if (c & 2u) atomicAdd(nR + nd, 1u);
+    }
 }
 
 // per level node: sizes that the three scans turn into offsets
@@ -291,8 +332,41 @@ __global__ void scatter_kernel(const LevelNode* __restrict__ nodes, const Decisi
                                uint32_t* __restrict__ nextTri, uint32_t* __restrict__ nextNode, uint32_t leafIdBase, const uint32_t* __restrict__ leafRefOff,
                                uint32_t* __restrict__ leafCursor, uint32_t* __restrict__ leafIds) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nRefs) return;
-    const uint32_t nd = refNode[i], t = refTri[i];
+    const bool valid = i < nRefs;
+    const uint32_t nd = valid ? refNode[i] : 0xFFFFFFFFu;
+    const bool uniform = warp_same_node(valid, nd);
+    const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+    if (uniform) {   // one node for the whole warp: one atomic per destination, the lanes take consecutive places
+        const uint32_t t = refTri[i];
+        const Decision d = dec[nd];
+        if (d.axis < 0) {
+            uint32_t base = 0;
+            if (lane == 0u) base = atomicAdd(leafCursor + nd, 32u);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            leafIds[leafIdBase + leafRefOff[nd] + base + lane] = t;
+            return;
+        }
+        const uint32_t c = classify(nodes[nd], d, triLo[t], triHi[t]);
+        const uint32_t r = splitRank[nd];
+        const uint32_t ml = __ballot_sync(0xFFFFFFFFu, (c & 1u) != 0u), mr = __ballot_sync(0xFFFFFFFFu, (c & 2u) != 0u);
+        uint32_t bl = 0, br = 0;
+        if (lane == 0u) {
+            if (ml) bl = atomicAdd(cursor + 2u * r, static_cast<uint32_t>(__popc(ml)));
+            if (mr) br = atomicAdd(cursor + 2u * r + 1u, static_cast<uint32_t>(__popc(mr)));
+        }
+        bl = __shfl_sync(0xFFFFFFFFu, bl, 0); br = __shfl_sync(0xFFFFFFFFu, br, 0);
+        if (c & 1u) {
+            const uint32_t p = next[2u * r].begin + bl + __popc(ml & below);
+            nextTri[p] = t; nextNode[p] = 2u * r;
+        }
+        if (c & 2u) {
+            const uint32_t p = next[2u * r + 1u].begin + br + __popc(mr & below);
+            nextTri[p] = t; nextNode[p] = 2u * r + 1u;
+        }
+        return;
+    }
+    if (!valid) return;
+    const uint32_t t = refTri[i];
     const Decision d = dec[nd];
     if (d.axis < 0) {
         leafIds[leafIdBase + leafRefOff[nd] + atomicAdd(leafCursor + nd, 1u)] = t;
@@ -521,12 +595,14 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
         cub::DeviceScan::ExclusiveSum(nullptr, tmp, static_cast<uint32_t*>(nullptr), static_cast<uint32_t*>(nullptr), static_cast<int>(2 * levelCap + 1), s);
         const size_t need = scene.vertices.size() * 4 + scene.triangles.size() * 4 + 32ull * nT + 4 * refCap * 4 + 2 * (2 * levelCap) * sizeof(LevelNode) +
                             2 * levelCap * sizeof(Decision) + 12 * (2 * levelCap + 1) * 4 + (4 * levelCap + 2) * 4 + (refCap / kSmall + 2) * (3 * 2 * kBins * 4 + 8) +
-                            nodeCap * (4 * 4 + 24 + 4) + refCap * 4 + tmp + 256 + 64 * 256 +
+                            nodeCap * (4 * 4 + 24 + 4) + refCap * 4 + tmp + 256 + 128 * 256 + 2 * kBoxBlocks * 16 +
                             (pack ? scene.normals.size() * 4 + nodeCap * (5 * 4 + 24) + 16 * 256 : 0);
         GK_CHECK(reserve_arena(need));
     }
     GK_CHECK(dVerts.alloc(scene.vertices.size())); GK_CHECK(dTris.alloc(scene.triangles.size()));
     GK_CHECK(triLo.alloc(nT)); GK_CHECK(triHi.alloc(nT));
+    Dev<float4> partLo, partHi;
+    GK_CHECK(partLo.alloc(kBoxBlocks)); GK_CHECK(partHi.alloc(kBoxBlocks));
     for (int i = 0; i < 2; ++i) { GK_CHECK(refTri[i].alloc(refCap)); GK_CHECK(refNode[i].alloc(refCap)); GK_CHECK(level[i].alloc(2 * levelCap)); }
     GK_CHECK(dec.alloc(2 * levelCap));
     for (Dev<uint32_t>* d : {&nL, &nR, &isSplit, &childRefs, &leafRefs, &splitRank, &childRefOff, &leafRefOff, &leafCursor, &isBig, &bigRank, &binSlot})
@@ -547,7 +623,8 @@ bool build_gpu_tree_with(const HostScene& scene, HostTree& out, std::string& err
     const unsigned B = 256;
     auto grid = [&](size_t n) { return static_cast<unsigned>((n + B - 1) / B); };
     tri_bounds_kernel<<<grid(nT), B, 0, s>>>(dVerts.p, dTris.p, nT, triLo.p, triHi.p, refTri[0].p, refNode[0].p);
-    scene_box_kernel<<<1, 256, 0, s>>>(triLo.p, triHi.p, nT, level[0].p);
+    scene_box_kernel<<<kBoxBlocks, 256, 0, s>>>(triLo.p, triHi.p, nT, nullptr, partLo.p, partHi.p, 0u);
+    scene_box_kernel<<<1, 256, 0, s>>>(partLo.p, partHi.p, kBoxBlocks, level[0].p, nullptr, nullptr, nT);
 
     uint32_t nNodes = 1, nRefs = nT, levelBase = 0, leafIdBase = 0, depthReached = 0;
     std::vector<std::pair<uint32_t, uint32_t>> levels;   // (first node, node count) of every depth, for the device pack
