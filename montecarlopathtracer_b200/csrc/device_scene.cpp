@@ -23,11 +23,28 @@ static void collect_emitters(const HostScene& scene, PackedScene& out, std::vect
     out.emitters.clear();
     areas.clear();
     areaSum = 0.0;
-    for (size_t t = 0; t < nT; ++t) {  // emitters keep triangle order: sequential
+    // which materials emit (rtx.hlsl:330: any Ka component > 0), then the emitting triangles in triangle order: the scan over the
+    // triangles' material ids runs in parallel for large scenes (static chunks, concatenated in chunk order)
+    std::vector<unsigned char> emits(scene.num_materials(), 0);
+    for (size_t m = 0; m < emits.size(); ++m) {
+        const float* Ka = &scene.materials[12 * m];
+        emits[m] = (Ka[0] > 0 || Ka[1] > 0 || Ka[2] > 0) ? 1 : 0;
+    }
+    std::vector<size_t> ids;
+    if (nT > 65536) {
+        const int chunks = 64;
+        std::vector<std::vector<size_t>> part(chunks);
+#pragma omp parallel for schedule(static, 1)
+        for (int c = 0; c < chunks; ++c)
+            for (size_t t = nT * c / chunks; t < nT * (c + 1) / chunks; ++t)
+                if (emits[scene.triangles[7 * t + 6]]) part[c].push_back(t);
+        for (const auto& p : part) ids.insert(ids.end(), p.begin(), p.end());
+    } else {
+        for (size_t t = 0; t < nT; ++t)
+            if (emits[scene.triangles[7 * t + 6]]) ids.push_back(t);
+    }
+    for (const size_t t : ids) {
         const uint32_t* r = &scene.triangles[7 * t];
-        // Emitter iff any Ka component > 0 (rtx.hlsl:330).
-        const float* Ka = &scene.materials[12 * static_cast<size_t>(r[6])];
-        if (!(Ka[0] > 0 || Ka[1] > 0 || Ka[2] > 0)) continue;
         const float* a = &scene.vertices[3 * static_cast<size_t>(r[0])];
         const float* b = &scene.vertices[3 * static_cast<size_t>(r[1])];
         const float* c = &scene.vertices[3 * static_cast<size_t>(r[2])];

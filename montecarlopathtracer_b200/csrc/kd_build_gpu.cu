@@ -104,26 +104,41 @@ __global__ void scene_box_kernel(const float4* __restrict__ triLo, const float4*
 __global__ void bin_kernel(const LevelNode* __restrict__ nodes, const uint32_t* __restrict__ refTri, const uint32_t* __restrict__ refNode,
                            uint32_t nRefs, const float4* __restrict__ triLo, const float4* __restrict__ triHi,
                            const uint32_t* __restrict__ binSlot, uint32_t* __restrict__ bins) {
+    // A node's references are contiguous: most blocks work on one node.  The block counts that node (the node of its first
+    // reference) in shared memory and adds the 192 totals to the global histogram once; other nodes' references go there directly.
+    __shared__ uint32_t sh[3 * 2 * kBins];
+    __shared__ uint32_t leadNode;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nRefs) return;
-    const uint32_t nd = refNode[i];
-    const uint32_t slot = binSlot[nd];
-    if (slot == 0xFFFFFFFFu) return;   // small node: exact sweep in split_kernel
-    const LevelNode n = nodes[nd];
-    const float4 a = triLo[refTri[i]], b = triHi[refTri[i]];
-    const float tlo[3] = {a.x, a.y, a.z}, thi[3] = {b.x, b.y, b.z};
-    uint32_t* base = bins + static_cast<size_t>(slot) * (3 * 2 * kBins);
+    for (uint32_t k = threadIdx.x; k < 3 * 2 * kBins; k += blockDim.x) sh[k] = 0u;
+    if (threadIdx.x == 0) leadNode = refNode[blockIdx.x * blockDim.x];
+    __syncthreads();
+    const uint32_t lead = leadNode;
+    if (i < nRefs) {
+        const uint32_t nd = refNode[i];
+        const uint32_t slot = binSlot[nd];
+        if (slot != 0xFFFFFFFFu) {   // else small node: exact sweep in split_kernel
+            const LevelNode n = nodes[nd];
+            const float4 a = triLo[refTri[i]], b = triHi[refTri[i]];
+            const float tlo[3] = {a.x, a.y, a.z}, thi[3] = {b.x, b.y, b.z};
+            uint32_t* base = nd == lead ? sh : bins + static_cast<size_t>(slot) * (3 * 2 * kBins);
 #pragma unroll
-    for (int ax = 0; ax < 3; ++ax) {
-        const float w = n.hi[ax] - n.lo[ax];
-        if (!(w > 0.0f)) continue;
-        const float s = static_cast<float>(kBins) / w;
-        const float lo = fmaxf(tlo[ax], n.lo[ax]), hi = fminf(thi[ax], n.hi[ax]);
-        const int bl = min(kBins - 1, max(0, static_cast<int>((lo - n.lo[ax]) * s)));
-        const int bh = min(kBins - 1, max(0, static_cast<int>((hi - n.lo[ax]) * s)));
-        atomicAdd(base + (ax * 2 + 0) * kBins + bl, 1u);
-        atomicAdd(base + (ax * 2 + 1) * kBins + bh, 1u);
+            for (int ax = 0; ax < 3; ++ax) {
+                const float w = n.hi[ax] - n.lo[ax];
+                if (!(w > 0.0f)) continue;
+                const float s = static_cast<float>(kBins) / w;
+                const float lo = fmaxf(tlo[ax], n.lo[ax]), hi = fminf(thi[ax], n.hi[ax]);
+                const int bl = min(kBins - 1, max(0, static_cast<int>((lo - n.lo[ax]) * s)));
+                const int bh = min(kBins - 1, max(0, static_cast<int>((hi - n.lo[ax]) * s)));
+                atomicAdd(base + (ax * 2 + 0) * kBins + bl, 1u);
+                atomicAdd(base + (ax * 2 + 1) * kBins + bh, 1u);
+            }
+        }
     }
+    __syncthreads();
+    const uint32_t leadSlot = binSlot[lead];
+    if (leadSlot != 0xFFFFFFFFu)
+        for (uint32_t k = threadIdx.x; k < 3 * 2 * kBins; k += blockDim.x)
+            if (sh[k]) atomicAdd(bins + static_cast<size_t>(leadSlot) * (3 * 2 * kBins) + k, sh[k]);
 }
 
 // One thread per level node: SAH over the binned planes (big nodes) or over every reference bound (small nodes).
@@ -167,21 +182,23 @@ __global__ void split_kernel(const LevelNode* __restrict__ nodes, uint32_t nNode
             }
         }
     } else {
+        // small node (<= kSmall references): every reference bound is a candidate plane, counted exactly against all references.
+        // The bounds cut to the cell are fetched once per axis into a local array; the n^2 comparisons then run on it.
+        float blo[kSmall], bhi[kSmall];
         for (int ax = 0; ax < 3; ++ax) {
             if (!(n.hi[ax] > n.lo[ax])) continue;
-            for (uint32_t i = n.begin; i < n.end; ++i) {
-                const uint32_t t = refTri[i];
+            for (uint32_t i = 0; i < cnt; ++i) {
+                const uint32_t t = refTri[n.begin + i];
                 const float4 a = triLo[t], b = triHi[t];
-                const float lo = fmaxf(ax == 0 ? a.x : (ax == 1 ? a.y : a.z), n.lo[ax]);
-                const float hi = fminf(ax == 0 ? b.x : (ax == 1 ? b.y : b.z), n.hi[ax]);
+                blo[i] = fmaxf(ax == 0 ? a.x : (ax == 1 ? a.y : a.z), n.lo[ax]);
+                bhi[i] = fminf(ax == 0 ? b.x : (ax == 1 ? b.y : b.z), n.hi[ax]);
+            }
+            for (uint32_t i = 0; i < cnt; ++i) {
                 for (int side = 0; side < 2; ++side) {
-                    const float s = side ? hi : lo;
+                    const float s = side ? bhi[i] : blo[i];
                     uint32_t nl = 0, nr = 0;
-                    for (uint32_t j = n.begin; j < n.end; ++j) {
-                        const uint32_t u = refTri[j];
-                        const float4 c = triLo[u], e = triHi[u];
-                        const float l2 = fmaxf(ax == 0 ? c.x : (ax == 1 ? c.y : c.z), n.lo[ax]);
-                        const float h2 = fminf(ax == 0 ? e.x : (ax == 1 ? e.y : e.z), n.hi[ax]);
+                    for (uint32_t j = 0; j < cnt; ++j) {
+                        const float l2 = blo[j], h2 = bhi[j];
                         if (l2 == h2 && l2 == s) { ++nl; continue; }   // flat on the plane: left only
                         nl += l2 < s ? 1u : 0u;
                         nr += h2 > s ? 1u : 0u;

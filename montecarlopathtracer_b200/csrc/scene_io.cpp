@@ -29,11 +29,21 @@ bool validate_scene(const HostScene& s, std::string& err) {
     if (s.num_triangles() == 0) { err = "scene has no triangles"; return false; }
     const uint32_t nV = static_cast<uint32_t>(s.num_vertices()), nN = static_cast<uint32_t>(s.num_normals()),
                    nM = static_cast<uint32_t>(s.num_materials());
-    for (size_t t = 0; t < s.num_triangles(); ++t) {
+    // first offending triangle (lowest index), found in parallel for large scenes
+    const long long nT = static_cast<long long>(s.num_triangles());
+    long long firstBad = nT;
+#pragma omp parallel for schedule(static) reduction(min : firstBad) if (nT > 65536)
+    for (long long t = 0; t < nT; ++t) {
+        const uint32_t* r = &s.triangles[7 * static_cast<size_t>(t)];
+        if (r[0] >= nV || r[1] >= nV || r[2] >= nV || r[3] >= nN || r[4] >= nN || r[5] >= nN || r[6] >= nM) firstBad = t < firstBad ? t : firstBad;
+    }
+    if (firstBad < nT) {
+        const size_t t = static_cast<size_t>(firstBad);
         const uint32_t* r = &s.triangles[7 * t];
         if (r[0] >= nV || r[1] >= nV || r[2] >= nV) { err = "triangle " + std::to_string(t) + ": vertex index out of range"; return false; }
         if (r[3] >= nN || r[4] >= nN || r[5] >= nN) { err = "triangle " + std::to_string(t) + ": normal index out of range"; return false; }
-        if (r[6] >= nM) { err = "triangle " + std::to_string(t) + ": material index out of range"; return false; }
+        err = "triangle " + std::to_string(t) + ": material index out of range";
+        return false;
     }
     return true;
 }
