@@ -147,6 +147,9 @@ def test_device_pack_equals_the_host_pack(gpu, scenes, name):
         a = T.render_scene(cfg); ra = T.counters().rays
         rays = np.random.default_rng(3).normal(size=(4096, 6)).astype(np.float32); rays[:, :3] *= 3; rays[:, 1] += 5
         hits_a = T.intersect_batch(rays, T.ISECT_ROPES)
+        T.set_tuning("verify_layout", 1)      # install-time self-check: host pack of the same tree, layout check, word-for-word comparison
+        T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_GPU)
+        T.set_tuning("verify_layout", 0)
         T.set_tuning("device_pack", 0)
         T.create_geometry(s.verts, s.normals, s.tris, s.mats, T.BUILD_GPU)
         assert T.compare_device_tables() == (0, 0, 0)
